@@ -1,0 +1,790 @@
+/* oracle/oracle.c -- TEST INFRASTRUCTURE (the CPU oracle), not product code.
+ *
+ * A plain-C restatement of the reference's differentiable Gaussian rasterizer
+ * (stu214634/gaussian-transformer, submodules/diff-gaussian-rasterization,
+ * abbreviated DGR below).  Only tests/, __graft_entry__.smoke() and the
+ * cpu_baseline / --impl reference legs of bench.py may load this; the product
+ * library (libgsrast.so) never does and has no CPU fallback.
+ *
+ * Parity pin: the reference ships no tests, golden vectors or fixtures
+ * (SURVEY.md section 4), so this oracle is pinned against OUTPUTS OF THE
+ * REFERENCE ITSELF: tests/golden/ holds fixtures produced by running the
+ * unmodified reference CUDA rasterizer (oracle/_ref, built by oracle/Makefile
+ * from the sources under /root/reference) on a B200 with
+ * tests/golden/make_golden.py; tests/test_oracle_golden.py checks this file
+ * against them (radii / tiles_touched / ranges / point_list bit-exact).
+ *
+ * Arithmetic notes.  The integer results of the path (radii, tile rectangles,
+ * sort order) are fp32 values pushed through ceil / truncation / a "== 0"
+ * test, so they depend on exactly where the reference's compiled code rounds.
+ * The forward per-Gaussian math below therefore follows the dataflow of the
+ * reference kernel as nvcc 12.9 compiled it for sm_100a (cuobjdump -sass of
+ * oracle/_ref/forward.o): fmaf() stands where the SASS has FFMA, a plain
+ * product/sum (this file is compiled with -ffp-contract=off) where it has
+ * FMUL/FADD.  Division and sqrt are IEEE-correct on both sides.  expf in the
+ * blend differs from CUDA's by <= 2 ulp (MUFU.EX2 cannot be restated), so
+ * images are compared with a tolerance, never bit-exactly.
+ *
+ * Reference lines followed by each function are cited at its head.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <stdio.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define TILE 16 /* DGR/cuda_rasterizer/config.h:16-17 BLOCK_X = BLOCK_Y = 16 */
+
+/* DGR/cuda_rasterizer/auxiliary.h:22-39 */
+static const float SH_C0 = 0.28209479177387814f;
+static const float SH_C1 = 0.4886025119029199f;
+static const float SH_C2[5] = {1.0925484305920792f, -1.0925484305920792f,
+                               0.31539156525252005f, -1.0925484305920792f,
+                               0.5462742152960396f};
+static const float SH_C3[7] = {-0.5900435899266435f, 2.890611442640554f,
+                               -0.4570457994644658f, 0.3731763325901154f,
+                               -0.4570457994644658f, 1.445305721320277f,
+                               -0.5900435899266435f};
+
+typedef struct OracleState {
+  int P, W, H, tiles_x, tiles_y;
+  long R;
+  /* geometry state (rasterizer_impl.h:29-45) */
+  float* depths;         /* P   */
+  unsigned char* clamped;/* 3P  */
+  float* means2D;        /* 2P  */
+  float* cov3D;          /* 6P  */
+  float* conic_opacity;  /* 4P  */
+  float* rgb;            /* 3P  */
+  uint32_t* tiles_touched;  /* P */
+  uint32_t* point_offsets;  /* P (inclusive scan) */
+  /* binning state (rasterizer_impl.h:55-65) */
+  uint64_t* keys_unsorted;
+  uint32_t* vals_unsorted;
+  uint64_t* keys;
+  uint32_t* point_list;
+  /* image state (rasterizer_impl.h:47-53) */
+  float* accum_alpha;   /* N */
+  uint32_t* n_contrib;  /* N */
+  uint32_t* ranges;     /* 2T */
+  long cap_P, cap_R, cap_N, cap_T;
+} OracleState;
+
+OracleState* orc_create(void) { return (OracleState*)calloc(1, sizeof(OracleState)); }
+
+static void orc_free_arrays(OracleState* s) {
+  free(s->depths); free(s->clamped); free(s->means2D); free(s->cov3D);
+  free(s->conic_opacity); free(s->rgb); free(s->tiles_touched);
+  free(s->point_offsets); free(s->keys_unsorted); free(s->vals_unsorted);
+  free(s->keys); free(s->point_list); free(s->accum_alpha); free(s->n_contrib);
+  free(s->ranges);
+}
+
+void orc_destroy(OracleState* s) {
+  if (!s) return;
+  orc_free_arrays(s);
+  free(s);
+}
+
+static void* xrealloc(void* p, size_t n) {
+  void* q = realloc(p, n ? n : 1);
+  if (!q) { fprintf(stderr, "oracle: out of memory (%zu bytes)\n", n); abort(); }
+  return q;
+}
+
+/* float -> int conversions with the saturating / NaN->0 behaviour of the
+ * GPU's F2I (the reference relies on it for non-finite inputs). */
+static int f2i_trunc(float v) {
+  if (isnan(v)) return 0;
+  if (v >= 2147483648.0f) return INT32_MAX;
+  if (v <= -2147483648.0f) return INT32_MIN;
+  return (int)v;
+}
+static int f2i_ceil(float v) { return f2i_trunc(ceilf(v)); }
+
+static inline int imin(int a, int b) { return a < b ? a : b; }
+static inline int imax(int a, int b) { return a > b ? a : b; }
+
+/* DGR/cuda_rasterizer/auxiliary.h:41-44 ndc2Pix -- evaluated in double; the
+ * compiled code contracts (v+1)*S-1 into one DFMA. */
+static float ndc2pix(float v, int S) {
+  double t = fma((double)v + 1.0, (double)S, -1.0);
+  return (float)(t * 0.5);
+}
+
+/* m0*x + m4*y + m8*z + m12 as compiled: FADD(FFMA(z,m8,FFMA(x,m0,FMUL(y,m4))),m12)
+ * (auxiliary.h:58-77 transformPoint4x3 / 4x4). */
+static inline float xf_row(const float* m, int r, float x, float y, float z) {
+  float t = y * m[4 + r];
+  t = fmaf(x, m[r], t);
+  t = fmaf(z, m[8 + r], t);
+  return t + m[12 + r];
+}
+
+/* a0*b0 + a1*b1 + a2*b2 as compiled for the mat3 products:
+ * FFMA(a2,b2,FFMA(a0,b0,FMUL(a1,b1))). */
+static inline float dot3c(float a0, float b0, float a1, float b1, float a2, float b2) {
+  return fmaf(a2, b2, fmaf(a0, b0, a1 * b1));
+}
+
+/* DGR/cuda_rasterizer/auxiliary.h:46-56 getRect */
+static void get_rect(float px, float py, int radius, int gx, int gy,
+                     int* minx, int* miny, int* maxx, int* maxy) {
+  float r = (float)radius;
+  *minx = imin(gx, imax(0, f2i_trunc((px - r) * 0.0625f)));
+  *miny = imin(gy, imax(0, f2i_trunc((py - r) * 0.0625f)));
+  *maxx = imin(gx, imax(0, f2i_trunc((((px + r) + 16.0f) - 1.0f) * 0.0625f)));
+  *maxy = imin(gy, imax(0, f2i_trunc((((py + r) + 16.0f) - 1.0f) * 0.0625f)));
+}
+
+/* DGR/cuda_rasterizer/forward.cu:118-152 computeCov3D.  M = S*R keeps the
+ * reference's multiplications by the zero entries of S (they turn non-finite
+ * rotation entries into NaN exactly as the reference does). */
+static void cov3d_from_scale_rot(const float* sc, float mod, const float* q, float* out) {
+  float r = q[0], x = q[1], y = q[2], z = q[3];
+  float xz = x * z, rx = r * x, rz = r * z, yy = y * y, zz = z * z;
+  float xz_p_ry = fmaf(r, y, xz), xz_m_ry = fmaf(-r, y, xz);
+  float yz_m_rx = fmaf(y, z, -rx), yz_p_rx = fmaf(y, z, rx);
+  float xy_m_rz = fmaf(x, y, -rz), xy_p_rz = fmaf(x, y, rz);
+  float xx_p_yy = fmaf(x, x, yy);
+  float yy_p_zz = yy + zz;
+  float xx_p_zz = fmaf(x, x, zz);
+  /* glm columns of R (forward.cu:134-138) */
+  float R00 = 1.0f - (yy_p_zz + yy_p_zz), R01 = xy_m_rz + xy_m_rz, R02 = xz_p_ry + xz_p_ry;
+  float R10 = xy_p_rz + xy_p_rz, R11 = 1.0f - (xx_p_zz + xx_p_zz), R12 = yz_m_rx + yz_m_rx;
+  float R20 = xz_m_ry + xz_m_ry, R21 = yz_p_rx + yz_p_rx, R22 = 1.0f - (xx_p_yy + xx_p_yy);
+  float sx = sc[0] * mod, sy = sc[1] * mod, sz = sc[2] * mod;
+  /* M[c][r] = S[r][r]*R[c][r] + 0*R[c][k1] + 0*R[c][k2] */
+  float A00 = fmaf(0.0f, R02, fmaf(0.0f, R01, sx * R00));
+  float A01 = fmaf(0.0f, R02, fmaf(sy, R01, 0.0f * R00));
+  float A02 = fmaf(sz, R02, fmaf(0.0f, R01, 0.0f * R00));
+  float A10 = fmaf(0.0f, R12, fmaf(sx, R10, 0.0f * R11));
+  float A11 = fmaf(0.0f, R12, fmaf(0.0f, R10, sy * R11));
+  float A12 = fmaf(sz, R12, fmaf(0.0f, R10, 0.0f * R11));
+  float A20 = fmaf(0.0f, R22, fmaf(sx, R20, 0.0f * R21));
+  float A21 = fmaf(0.0f, R22, fmaf(0.0f, R20, sy * R21));
+  float A22 = fmaf(sz, R22, fmaf(0.0f, R20, 0.0f * R21));
+  /* Sigma = M^T M, Sigma[c][r] = dot(col r, col c) */
+  out[0] = dot3c(A00, A00, A01, A01, A02, A02);
+  out[1] = dot3c(A00, A10, A01, A11, A02, A12);
+  out[2] = dot3c(A00, A20, A01, A21, A02, A22);
+  out[3] = dot3c(A10, A10, A11, A11, A12, A12);
+  out[4] = dot3c(A10, A20, A11, A21, A12, A22);
+  out[5] = dot3c(A20, A20, A21, A21, A22, A22);
+}
+
+/* DGR/cuda_rasterizer/forward.cu:74-113 computeCov2D.  Returns (a, b, c) with
+ * the 0.3 low-pass already added to a and c. */
+static void cov2d(const float* p, float fx, float fy, float tanx, float tany,
+                  const float* c3, const float* v, float* a, float* b, float* c) {
+  float tz = xf_row(v, 2, p[0], p[1], p[2]);
+  float tx = xf_row(v, 0, p[0], p[1], p[2]);
+  float ty = xf_row(v, 1, p[0], p[1], p[2]);
+  float limx = 1.3f * tanx, limy = 1.3f * tany;
+  float txtz = tx / tz, tytz = ty / tz;
+  float cx = fminf(limx, fmaxf(-limx, txtz));
+  float cy = fminf(limy, fmaxf(-limy, tytz));
+  float Jx = fx / tz;
+  float tz2 = tz * tz;
+  float J02 = ((tz * -cx) * fx) / tz2; /* -(fx * (cx*tz)) / (tz*tz) */
+  float Jy = fy / tz;
+  float J12 = ((tz * -cy) * fy) / tz2;
+  /* T = W*J (glm column-major), rows 0/1 of Jac*Rwc */
+  float T0[3], T1[3];
+  for (int r = 0; r < 3; r++) {
+    float w0 = v[4 * r + 0], w1 = v[4 * r + 1], w2 = v[4 * r + 2];
+    T0[r] = fmaf(w2, J02, fmaf(w0, Jx, 0.0f * w1));
+    T1[r] = fmaf(w2, J12, fmaf(0.0f, w0, w1 * Jy));
+  }
+  /* B[k][r] = sum_j T[r][j]*Vrk[j][k] ; cov[c][r] = sum_k B[k][r]*T[c][k] */
+  float V[3][3] = {{c3[0], c3[1], c3[2]}, {c3[1], c3[3], c3[4]}, {c3[2], c3[4], c3[5]}};
+  float B0[3], B1[3];
+  for (int k = 0; k < 3; k++) {
+    B0[k] = dot3c(T0[0], V[0][k], T0[1], V[1][k], T0[2], V[2][k]);
+    B1[k] = dot3c(T1[0], V[0][k], T1[1], V[1][k], T1[2], V[2][k]);
+  }
+  float c00 = dot3c(T0[0], B0[0], T0[1], B0[1], T0[2], B0[2]);
+  float c01 = dot3c(T0[0], B1[0], T0[1], B1[1], T0[2], B1[2]);
+  float c11 = dot3c(T1[0], B1[0], T1[1], B1[1], T1[2], B1[2]);
+  *a = c00 + 0.3f;
+  *b = c01;
+  *c = c11 + 0.3f;
+}
+
+/* DGR/cuda_rasterizer/forward.cu:20-71 computeColorFromSH (forward).  Only
+ * rgb depends on it (no integer result), so plain fp32 without contraction. */
+static void sh_to_rgb(int deg, int M, const float* pos, const float* cam,
+                      const float* sh, float* rgb, unsigned char* clamped) {
+  float dx = pos[0] - cam[0], dy = pos[1] - cam[1], dz = pos[2] - cam[2];
+  float len = sqrtf(fmaf(dz, dz, fmaf(dx, dx, dy * dy)));
+  float x = dx / len, y = dy / len, z = dz / len;
+  (void)M;
+  for (int c = 0; c < 3; c++) {
+    #define SH(k) sh[3 * (k) + c]
+    float r = SH_C0 * SH(0);
+    if (deg > 0) {
+      r = r - SH_C1 * y * SH(1) + SH_C1 * z * SH(2) - SH_C1 * x * SH(3);
+      if (deg > 1) {
+        float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        r = r + SH_C2[0] * xy * SH(4) + SH_C2[1] * yz * SH(5) +
+            SH_C2[2] * (2.0f * zz - xx - yy) * SH(6) + SH_C2[3] * xz * SH(7) +
+            SH_C2[4] * (xx - yy) * SH(8);
+        if (deg > 2) {
+          r = r + SH_C3[0] * y * (3.0f * xx - yy) * SH(9) + SH_C3[1] * xy * z * SH(10) +
+              SH_C3[2] * y * (4.0f * zz - xx - yy) * SH(11) +
+              SH_C3[3] * z * (2.0f * zz - 3.0f * xx - 3.0f * yy) * SH(12) +
+              SH_C3[4] * x * (4.0f * zz - xx - yy) * SH(13) +
+              SH_C3[5] * z * (xx - yy) * SH(14) + SH_C3[6] * x * (xx - 3.0f * yy) * SH(15);
+        }
+      }
+    }
+    #undef SH
+    r += 0.5f;
+    clamped[c] = (r < 0.0f);
+    rgb[c] = r < 0.0f ? 0.0f : r; /* glm::max(result, 0): NaN -> stays NaN?  max(NaN,0)=0 on GPU */
+    if (isnan(r)) rgb[c] = 0.0f;
+  }
+}
+
+/* DGR/cuda_rasterizer/rasterizer_impl.cu:35-50 getHigherMsb: number of bits
+ * needed so that (1 << bits) > n, found by bisection exactly like the reference
+ * (result for T tiles: 13 @1080p, 15 @4K, 11 @800x450). */
+static uint32_t higher_msb(uint32_t n) {
+  uint32_t msb = 16, step = 16;
+  while (step > 1) {
+    step /= 2;
+    if (n >> msb) msb += step; else msb -= step;
+  }
+  if (n >> msb) msb++;
+  return msb;
+}
+uint32_t orc_higher_msb(uint32_t n) { return higher_msb(n); }
+
+static void ensure(OracleState* s, long P, long N, long T) {
+  if (P > s->cap_P) {
+    s->depths = xrealloc(s->depths, 4 * P);
+    s->clamped = xrealloc(s->clamped, 3 * P);
+    s->means2D = xrealloc(s->means2D, 8 * P);
+    s->cov3D = xrealloc(s->cov3D, 24 * P);
+    s->conic_opacity = xrealloc(s->conic_opacity, 16 * P);
+    s->rgb = xrealloc(s->rgb, 12 * P);
+    s->tiles_touched = xrealloc(s->tiles_touched, 4 * P);
+    s->point_offsets = xrealloc(s->point_offsets, 4 * P);
+    s->cap_P = P;
+  }
+  if (N > s->cap_N) {
+    s->accum_alpha = xrealloc(s->accum_alpha, 4 * N);
+    s->n_contrib = xrealloc(s->n_contrib, 4 * N);
+    s->cap_N = N;
+  }
+  if (T > s->cap_T) {
+    s->ranges = xrealloc(s->ranges, 8 * T);
+    s->cap_T = T;
+  }
+}
+
+static void ensure_R(OracleState* s, long R) {
+  if (R > s->cap_R) {
+    s->keys_unsorted = xrealloc(s->keys_unsorted, 8 * R);
+    s->vals_unsorted = xrealloc(s->vals_unsorted, 4 * R);
+    s->keys = xrealloc(s->keys, 8 * R);
+    s->point_list = xrealloc(s->point_list, 4 * R);
+    s->cap_R = R;
+  }
+}
+
+/* Stable LSD radix sort of (key,value) pairs on key bits [0,nbits): the
+ * observable contract of cub::DeviceRadixSort::SortPairs as called at
+ * DGR/cuda_rasterizer/rasterizer_impl.cu:303-308. */
+static void radix_sort_pairs(uint64_t* kin, uint32_t* vin, uint64_t* kout,
+                             uint32_t* vout, long n, int nbits) {
+  uint64_t* ka = kin; uint32_t* va = vin; uint64_t* kb = kout; uint32_t* vb = vout;
+  size_t* cnt = (size_t*)malloc(sizeof(size_t) * 65537);
+  int passes = 0;
+  for (int shift = 0; shift < nbits; shift += 16) {
+    int bits = nbits - shift < 16 ? nbits - shift : 16;
+    uint64_t mask = ((uint64_t)1 << bits) - 1;
+    memset(cnt, 0, sizeof(size_t) * 65537);
+    for (long i = 0; i < n; i++) cnt[((ka[i] >> shift) & mask) + 1]++;
+    for (int d = 0; d < 65536; d++) cnt[d + 1] += cnt[d];
+    for (long i = 0; i < n; i++) {
+      size_t p = cnt[(ka[i] >> shift) & mask]++;
+      kb[p] = ka[i]; vb[p] = va[i];
+    }
+    uint64_t* tk = ka; ka = kb; kb = tk;
+    uint32_t* tv = va; va = vb; vb = tv;
+    passes++;
+  }
+  if (ka != kout) { memcpy(kout, ka, 8 * n); memcpy(vout, va, 4 * n); }
+  free(cnt);
+}
+
+/* Forward.  Mirrors CudaRasterizer::Rasterizer::forward
+ * (DGR/cuda_rasterizer/rasterizer_impl.cu:198-336):
+ *   preprocess (forward.cu:155-256) -> inclusive scan (:277) -> duplicateWithKeys
+ *   (:70-111) -> stable sort on 32+getHigherMsb(T) bits (:300-308) ->
+ *   identifyTileRanges (:116-138) -> renderCUDA (forward.cu:261-374).
+ * NULL pointers mean "absent" exactly as in the reference.  out_color is
+ * (3,H,W); radii is int[P].  Returns num_rendered, or -1 when it would not fit
+ * the reference's int. */
+long orc_forward(OracleState* s, int P, int D, int M, const float* bg, int W, int H,
+                 const float* means3D, const float* shs, const float* colors_precomp,
+                 const float* opacities, const float* scales, float scale_modifier,
+                 const float* rotations, const float* cov3D_precomp,
+                 const float* view, const float* proj, const float* campos,
+                 float tanfovx, float tanfovy, float* out_color, int* radii) {
+  const int gx = (W + TILE - 1) / TILE, gy = (H + TILE - 1) / TILE;
+  const long N = (long)W * H, T = (long)gx * gy;
+  const float focal_y = H / (2.0f * tanfovy), focal_x = W / (2.0f * tanfovx);
+  s->P = P; s->W = W; s->H = H; s->tiles_x = gx; s->tiles_y = gy; s->R = 0;
+  memset(out_color, 0, sizeof(float) * 3 * N);
+  if (P == 0) return 0; /* rasterize_points.cu:80-114: image stays 0, not bg */
+  ensure(s, P, N, T);
+
+  #pragma omp parallel for schedule(static)
+  for (int i = 0; i < P; i++) {
+    radii[i] = 0;
+    s->tiles_touched[i] = 0;
+    const float* p = means3D + 3 * (long)i;
+    /* auxiliary.h:139-164 in_frustum */
+    float vz = xf_row(view, 2, p[0], p[1], p[2]);
+    if (vz <= 0.2f) continue; /* NaN passes, as in the reference (FSETP.GTU) */
+    float hw = xf_row(proj, 3, p[0], p[1], p[2]);
+    float hx = xf_row(proj, 0, p[0], p[1], p[2]);
+    float hy = xf_row(proj, 1, p[0], p[1], p[2]);
+    float pw = 1.0f / (hw + 0.0000001f);
+    float projx = hx * pw, projy = hy * pw;
+    const float* c3;
+    if (cov3D_precomp) c3 = cov3D_precomp + 6 * (long)i;
+    else {
+      cov3d_from_scale_rot(scales + 3 * (long)i, scale_modifier, rotations + 4 * (long)i,
+                           s->cov3D + 6 * (long)i);
+      c3 = s->cov3D + 6 * (long)i;
+    }
+    float a, b, c;
+    cov2d(p, focal_x, focal_y, tanfovx, tanfovy, c3, view, &a, &b, &c);
+    float det = fmaf(a, c, -(b * b));
+    if (det == 0.0f) continue;
+    float det_inv = 1.0f / det;
+    float conx = c * det_inv, cony = b * -det_inv, conz = a * det_inv;
+    float mid = (a + c) * 0.5f;
+    float disc = fmaxf(fmaf(mid, mid, -det), 0.1f);
+    float sq = sqrtf(disc);
+    float l1 = mid + sq, l2 = mid - sq;
+    float lmax = fmaxf(l1, l2);
+    int my_radius = f2i_ceil(sqrtf(lmax) * 3.0f);
+    float px = ndc2pix(projx, W), py = ndc2pix(projy, H);
+    int minx, miny, maxx, maxy;
+    get_rect(px, py, my_radius, gx, gy, &minx, &miny, &maxx, &maxy);
+    if ((maxx - minx) * (maxy - miny) == 0) continue;
+    if (!colors_precomp)
+      sh_to_rgb(D, M, p, campos, shs + 3 * (long)M * i, s->rgb + 3 * (long)i,
+                s->clamped + 3 * (long)i);
+    s->depths[i] = vz;
+    radii[i] = my_radius;
+    s->means2D[2 * (long)i] = px; s->means2D[2 * (long)i + 1] = py;
+    float* co = s->conic_opacity + 4 * (long)i;
+    co[0] = conx; co[1] = cony; co[2] = conz; co[3] = opacities[i];
+    s->tiles_touched[i] = (uint32_t)((maxy - miny) * (maxx - minx));
+  }
+
+  /* rasterizer_impl.cu:277-281 */
+  uint64_t run = 0;
+  for (int i = 0; i < P; i++) { run += s->tiles_touched[i]; s->point_offsets[i] = (uint32_t)run; }
+  if (run > 0x7fffffffULL) return -1;
+  long R = (long)run;
+  s->R = R;
+  ensure_R(s, R);
+
+  /* rasterizer_impl.cu:70-111 duplicateWithKeys */
+  #pragma omp parallel for schedule(dynamic, 1024)
+  for (int i = 0; i < P; i++) {
+    if (radii[i] <= 0) continue;
+    long off = i == 0 ? 0 : s->point_offsets[i - 1];
+    int minx, miny, maxx, maxy;
+    get_rect(s->means2D[2 * (long)i], s->means2D[2 * (long)i + 1], radii[i], gx, gy,
+             &minx, &miny, &maxx, &maxy);
+    uint32_t dbits; memcpy(&dbits, &s->depths[i], 4);
+    for (int y = miny; y < maxy; y++)
+      for (int x = minx; x < maxx; x++) {
+        uint64_t key = (uint64_t)(y * gx + x);
+        s->keys_unsorted[off] = (key << 32) | dbits;
+        s->vals_unsorted[off] = (uint32_t)i;
+        off++;
+      }
+  }
+  int bit = (int)higher_msb((uint32_t)T);
+  radix_sort_pairs(s->keys_unsorted, s->vals_unsorted, s->keys, s->point_list, R, 32 + bit);
+
+  /* rasterizer_impl.cu:116-138 identifyTileRanges (+ memset :310) */
+  memset(s->ranges, 0, 8 * T);
+  for (long i = 0; i < R; i++) {
+    uint32_t t = (uint32_t)(s->keys[i] >> 32);
+    if (i == 0) s->ranges[2 * t] = 0;
+    else {
+      uint32_t pt = (uint32_t)(s->keys[i - 1] >> 32);
+      if (t != pt) { s->ranges[2 * pt + 1] = (uint32_t)i; s->ranges[2 * t] = (uint32_t)i; }
+    }
+    if (i == R - 1) s->ranges[2 * t + 1] = (uint32_t)R;
+  }
+
+  /* forward.cu:261-374 renderCUDA, one (tile,pixel) at a time */
+  const float* feat = colors_precomp ? colors_precomp : s->rgb;
+  #pragma omp parallel for schedule(dynamic, 4)
+  for (long t = 0; t < T; t++) {
+    int tx = (int)(t % gx), ty = (int)(t / gx);
+    uint32_t r0 = s->ranges[2 * t], r1 = s->ranges[2 * t + 1];
+    for (int ly = 0; ly < TILE; ly++)
+      for (int lx = 0; lx < TILE; lx++) {
+        int pxi = tx * TILE + lx, pyi = ty * TILE + ly;
+        if (pxi >= W || pyi >= H) continue;
+        long pix = (long)pyi * W + pxi;
+        float pfx = (float)pxi, pfy = (float)pyi;
+        float Tr = 1.0f, C0 = 0, C1 = 0, C2 = 0;
+        uint32_t contributor = 0, last = 0;
+        for (uint32_t k = r0; k < r1; k++) {
+          contributor++;
+          uint32_t id = s->point_list[k];
+          float dx = s->means2D[2 * (long)id] - pfx, dy = s->means2D[2 * (long)id + 1] - pfy;
+          const float* co = s->conic_opacity + 4 * (long)id;
+          /* SASS dataflow: FFMA(FFMA(dx, dx*A, dy*(dy*C)), -0.5, -(dy*(dx*B))) */
+          float t1 = dy * (dy * co[2]);
+          float sacc = fmaf(dx, dx * co[0], t1);
+          float v = dy * (dx * co[1]);
+          float power = fmaf(sacc, -0.5f, -v);
+          if (power > 0.0f) continue;
+          float alpha = fminf(0.99f, co[3] * expf(power));
+          if (alpha < 1.0f / 255.0f) continue;
+          float test_T = Tr * (1.0f - alpha);
+          if (test_T < 0.0001f) break;
+          const float* f = feat + 3 * (long)id;
+          C0 = fmaf(Tr, alpha * f[0], C0);
+          C1 = fmaf(Tr, alpha * f[1], C1);
+          C2 = fmaf(Tr, alpha * f[2], C2);
+          Tr = test_T;
+          last = contributor;
+        }
+        s->accum_alpha[pix] = Tr;
+        s->n_contrib[pix] = last;
+        out_color[pix] = fmaf(bg[0], Tr, C0);
+        out_color[N + pix] = fmaf(bg[1], Tr, C1);
+        out_color[2 * N + pix] = fmaf(bg[2], Tr, C2);
+      }
+  }
+  return R;
+}
+
+/* Accessors used by tests (decoded internal state). */
+const float* orc_depths(OracleState* s) { return s->depths; }
+const float* orc_means2D(OracleState* s) { return s->means2D; }
+const float* orc_cov3D(OracleState* s) { return s->cov3D; }
+const float* orc_conic_opacity(OracleState* s) { return s->conic_opacity; }
+const float* orc_rgb(OracleState* s) { return s->rgb; }
+const unsigned char* orc_clamped(OracleState* s) { return s->clamped; }
+const uint32_t* orc_tiles_touched(OracleState* s) { return s->tiles_touched; }
+const uint32_t* orc_point_offsets(OracleState* s) { return s->point_offsets; }
+const uint64_t* orc_keys(OracleState* s) { return s->keys; }
+const uint32_t* orc_point_list(OracleState* s) { return s->point_list; }
+const float* orc_final_T(OracleState* s) { return s->accum_alpha; }
+const uint32_t* orc_n_contrib(OracleState* s) { return s->n_contrib; }
+const uint32_t* orc_ranges(OracleState* s) { return s->ranges; }
+long orc_num_rendered(OracleState* s) { return s->R; }
+
+/* ------------------------------------------------------------------ backward */
+
+static inline void atomic_add_d(double* p, double v) {
+  #pragma omp atomic
+  *p += v;
+}
+
+/* Backward.  Mirrors CudaRasterizer::Rasterizer::backward
+ * (rasterizer_impl.cu:340-434): BACKWARD::render (backward.cu:399-557), then
+ * computeCov2DCUDA (:144-274) and preprocessCUDA (:346-396).  Uses the state
+ * left by the preceding orc_forward on the same OracleState.  The reference
+ * accumulates the per-pair terms with fp32 atomics in a nondeterministic
+ * order; here they are summed in double and rounded once (gradient parity is
+ * a tolerance check, 1e-3 relative).  All outputs are fully written (zeros
+ * where the reference's zero-initialised tensors stay untouched).
+ * Shapes: dL_dmean2D (P,3), dL_dconic (P,4) [.x .y unused .w], dL_dopacity (P),
+ * dL_dcolor (P,3), dL_dmean3D (P,3), dL_dcov3D (P,6), dL_dsh (P,M,3),
+ * dL_dscale (P,3), dL_drot (P,4). */
+void orc_backward(OracleState* s, int P, int D, int M, const float* bg, int W, int H,
+                  const float* means3D, const float* shs, const float* colors_precomp,
+                  const float* scales, float scale_modifier, const float* rotations,
+                  const float* cov3D_precomp, const float* view, const float* proj,
+                  const float* campos, float tanfovx, float tanfovy, const int* radii,
+                  const float* dL_dpix, float* dL_dmean2D, float* dL_dconic,
+                  float* dL_dopacity, float* dL_dcolor, float* dL_dmean3D,
+                  float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot) {
+  const int gx = s->tiles_x, gy = s->tiles_y;
+  const long N = (long)W * H, T = (long)gx * gy;
+  memset(dL_dmean2D, 0, 12 * (size_t)P); memset(dL_dconic, 0, 16 * (size_t)P);
+  memset(dL_dopacity, 0, 4 * (size_t)P); memset(dL_dcolor, 0, 12 * (size_t)P);
+  memset(dL_dmean3D, 0, 12 * (size_t)P); memset(dL_dcov3D, 0, 24 * (size_t)P);
+  if (M > 0 && dL_dsh) memset(dL_dsh, 0, 12 * (size_t)M * P);
+  memset(dL_dscale, 0, 12 * (size_t)P); memset(dL_drot, 0, 16 * (size_t)P);
+  if (P == 0) return;
+  double* acc = (double*)calloc((size_t)P * 9, sizeof(double));
+  const float* feat = colors_precomp ? colors_precomp : s->rgb;
+  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+
+  /* backward.cu:399-557 renderCUDA: per pixel, back to front */
+  #pragma omp parallel for schedule(dynamic, 4)
+  for (long t = 0; t < T; t++) {
+    int tx = (int)(t % gx), ty = (int)(t / gx);
+    uint32_t r0 = s->ranges[2 * t], r1 = s->ranges[2 * t + 1];
+    for (int ly = 0; ly < TILE; ly++)
+      for (int lx = 0; lx < TILE; lx++) {
+        int pxi = tx * TILE + lx, pyi = ty * TILE + ly;
+        if (pxi >= W || pyi >= H) continue;
+        long pix = (long)pyi * W + pxi;
+        float pfx = (float)pxi, pfy = (float)pyi;
+        const float T_final = s->accum_alpha[pix];
+        float Tr = T_final;
+        uint32_t last = s->n_contrib[pix];
+        float g0 = dL_dpix[pix], g1 = dL_dpix[N + pix], g2 = dL_dpix[2 * N + pix];
+        float dLp[3] = {g0, g1, g2};
+        float accum_rec[3] = {0, 0, 0}, last_color[3] = {0, 0, 0}, last_alpha = 0;
+        float bg_dot = 0;
+        for (int c = 0; c < 3; c++) bg_dot += bg[c] * dLp[c];
+        for (uint32_t j = last; j-- > 0;) {
+          uint32_t id = s->point_list[r0 + j];
+          (void)r1;
+          float dx = s->means2D[2 * (long)id] - pfx, dy = s->means2D[2 * (long)id + 1] - pfy;
+          const float* co = s->conic_opacity + 4 * (long)id;
+          float power = -0.5f * (co[0] * dx * dx + co[2] * dy * dy) - co[1] * dx * dy;
+          if (power > 0.0f) continue;
+          float G = expf(power);
+          float alpha = fminf(0.99f, co[3] * G);
+          if (alpha < 1.0f / 255.0f) continue;
+          Tr = Tr / (1.0f - alpha);
+          float dchannel_dcolor = alpha * Tr;
+          float dL_dalpha = 0;
+          double* a = acc + 9 * (size_t)id;
+          for (int c = 0; c < 3; c++) {
+            float col = feat[3 * (long)id + c];
+            accum_rec[c] = last_alpha * last_color[c] + (1.0f - last_alpha) * accum_rec[c];
+            last_color[c] = col;
+            dL_dalpha += (col - accum_rec[c]) * dLp[c];
+            atomic_add_d(&a[c], (double)(dchannel_dcolor * dLp[c]));
+          }
+          dL_dalpha *= Tr;
+          last_alpha = alpha;
+          dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot;
+          float dL_dG = co[3] * dL_dalpha;
+          float gdx = G * dx, gdy = G * dy;
+          float dG_ddelx = -gdx * co[0] - gdy * co[1];
+          float dG_ddely = -gdy * co[2] - gdx * co[1];
+          atomic_add_d(&a[3], (double)(dL_dG * dG_ddelx * ddelx_dx));
+          atomic_add_d(&a[4], (double)(dL_dG * dG_ddely * ddely_dy));
+          atomic_add_d(&a[5], (double)(-0.5f * gdx * dx * dL_dG));
+          atomic_add_d(&a[6], (double)(-0.5f * gdx * dy * dL_dG));
+          atomic_add_d(&a[7], (double)(-0.5f * gdy * dy * dL_dG));
+          atomic_add_d(&a[8], (double)(G * dL_dalpha));
+        }
+      }
+  }
+  for (long i = 0; i < P; i++) {
+    const double* a = acc + 9 * i;
+    dL_dcolor[3 * i] = (float)a[0]; dL_dcolor[3 * i + 1] = (float)a[1]; dL_dcolor[3 * i + 2] = (float)a[2];
+    dL_dmean2D[3 * i] = (float)a[3]; dL_dmean2D[3 * i + 1] = (float)a[4];
+    dL_dconic[4 * i] = (float)a[5]; dL_dconic[4 * i + 1] = (float)a[6]; dL_dconic[4 * i + 3] = (float)a[7];
+    dL_dopacity[i] = (float)a[8];
+  }
+  free(acc);
+
+  /* per-Gaussian part: backward.cu:144-274 then :346-396 */
+  const float h_x = W / (2.0f * tanfovx), h_y = H / (2.0f * tanfovy);
+  #pragma omp parallel for schedule(static)
+  for (int i = 0; i < P; i++) {
+    if (!(radii[i] > 0)) continue;
+    const float* p = means3D + 3 * (long)i;
+    const float* c3 = cov3D_precomp ? cov3D_precomp + 6 * (long)i : s->cov3D + 6 * (long)i;
+    float dcx = dL_dconic[4 * (long)i], dcy = dL_dconic[4 * (long)i + 1], dcz = dL_dconic[4 * (long)i + 3];
+    float tx = xf_row(view, 0, p[0], p[1], p[2]);
+    float ty = xf_row(view, 1, p[0], p[1], p[2]);
+    float tz = xf_row(view, 2, p[0], p[1], p[2]);
+    const float limx = 1.3f * tanfovx, limy = 1.3f * tanfovy;
+    const float txtz = tx / tz, tytz = ty / tz;
+    tx = fminf(limx, fmaxf(-limx, txtz)) * tz;
+    ty = fminf(limy, fmaxf(-limy, tytz)) * tz;
+    const float xgm = (txtz < -limx || txtz > limx) ? 0.0f : 1.0f;
+    const float ygm = (tytz < -limy || tytz > limy) ? 0.0f : 1.0f;
+    const float Jx = h_x / tz, Jy = h_y / tz;
+    const float J02 = -(h_x * tx) / (tz * tz), J12 = -(h_y * ty) / (tz * tz);
+    float T0[3], T1[3];
+    for (int k = 0; k < 3; k++) {
+      T0[k] = view[4 * k] * Jx + view[4 * k + 2] * J02;
+      T1[k] = view[4 * k + 1] * Jy + view[4 * k + 2] * J12;
+    }
+    const float V[3][3] = {{c3[0], c3[1], c3[2]}, {c3[1], c3[3], c3[4]}, {c3[2], c3[4], c3[5]}};
+    float TV0[3], TV1[3]; /* (T row) * Vrk */
+    for (int k = 0; k < 3; k++) {
+      TV0[k] = T0[0] * V[k][0] + T0[1] * V[k][1] + T0[2] * V[k][2];
+      TV1[k] = T1[0] * V[k][0] + T1[1] * V[k][1] + T1[2] * V[k][2];
+    }
+    float a = T0[0] * TV0[0] + T0[1] * TV0[1] + T0[2] * TV0[2] + 0.3f;
+    float b = T0[0] * TV1[0] + T0[1] * TV1[1] + T0[2] * TV1[2];
+    float c = T1[0] * TV1[0] + T1[1] * TV1[1] + T1[2] * TV1[2] + 0.3f;
+    float denom = a * c - b * b;
+    float dL_da = 0, dL_db = 0, dL_dc = 0;
+    float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+    float* dcov = dL_dcov3D + 6 * (long)i;
+    if (denom2inv != 0) {
+      dL_da = denom2inv * (-c * c * dcx + 2 * b * c * dcy + (denom - a * c) * dcz);
+      dL_dc = denom2inv * (-a * a * dcz + 2 * a * b * dcy + (denom - a * c) * dcx);
+      dL_db = denom2inv * 2 * (b * c * dcx - (denom + 2 * b * b) * dcy + a * b * dcz);
+      dcov[0] = T0[0] * T0[0] * dL_da + T0[0] * T1[0] * dL_db + T1[0] * T1[0] * dL_dc;
+      dcov[3] = T0[1] * T0[1] * dL_da + T0[1] * T1[1] * dL_db + T1[1] * T1[1] * dL_dc;
+      dcov[5] = T0[2] * T0[2] * dL_da + T0[2] * T1[2] * dL_db + T1[2] * T1[2] * dL_dc;
+      dcov[1] = 2 * T0[0] * T0[1] * dL_da + (T0[0] * T1[1] + T0[1] * T1[0]) * dL_db + 2 * T1[0] * T1[1] * dL_dc;
+      dcov[2] = 2 * T0[0] * T0[2] * dL_da + (T0[0] * T1[2] + T0[2] * T1[0]) * dL_db + 2 * T1[0] * T1[2] * dL_dc;
+      dcov[4] = 2 * T0[2] * T0[1] * dL_da + (T0[1] * T1[2] + T0[2] * T1[1]) * dL_db + 2 * T1[1] * T1[2] * dL_dc;
+    }
+    float dT0[3], dT1[3];
+    for (int k = 0; k < 3; k++) {
+      dT0[k] = 2 * TV0[k] * dL_da + TV1[k] * dL_db;
+      dT1[k] = 2 * TV1[k] * dL_dc + TV0[k] * dL_db;
+    }
+    float dJ00 = view[0] * dT0[0] + view[4] * dT0[1] + view[8] * dT0[2];
+    float dJ02 = view[2] * dT0[0] + view[6] * dT0[1] + view[10] * dT0[2];
+    float dJ11 = view[1] * dT1[0] + view[5] * dT1[1] + view[9] * dT1[2];
+    float dJ12 = view[2] * dT1[0] + view[6] * dT1[1] + view[10] * dT1[2];
+    float itz = 1.0f / tz, itz2 = itz * itz, itz3 = itz2 * itz;
+    float dtx = xgm * -h_x * itz2 * dJ02;
+    float dty = ygm * -h_y * itz2 * dJ12;
+    float dtz = -h_x * itz2 * dJ00 - h_y * itz2 * dJ11 + (2 * h_x * tx) * itz3 * dJ02 + (2 * h_y * ty) * itz3 * dJ12;
+    float dm[3];
+    dm[0] = view[0] * dtx + view[1] * dty + view[2] * dtz;
+    dm[1] = view[4] * dtx + view[5] * dty + view[6] * dtz;
+    dm[2] = view[8] * dtx + view[9] * dty + view[10] * dtz;
+
+    /* backward.cu:366-385: projection part */
+    float hx = proj[0] * p[0] + proj[4] * p[1] + proj[8] * p[2] + proj[12];
+    float hy = proj[1] * p[0] + proj[5] * p[1] + proj[9] * p[2] + proj[13];
+    float hw = proj[3] * p[0] + proj[7] * p[1] + proj[11] * p[2] + proj[15];
+    float m_w = 1.0f / (hw + 0.0000001f);
+    float mul1 = hx * m_w * m_w, mul2 = hy * m_w * m_w;
+    float g2x = dL_dmean2D[3 * (long)i], g2y = dL_dmean2D[3 * (long)i + 1];
+    dm[0] += (proj[0] * m_w - proj[3] * mul1) * g2x + (proj[1] * m_w - proj[3] * mul2) * g2y;
+    dm[1] += (proj[4] * m_w - proj[7] * mul1) * g2x + (proj[5] * m_w - proj[7] * mul2) * g2y;
+    dm[2] += (proj[8] * m_w - proj[11] * mul1) * g2x + (proj[9] * m_w - proj[11] * mul2) * g2y;
+
+    /* backward.cu:20-139 computeColorFromSH backward */
+    if (shs) {
+      float dox = p[0] - campos[0], doy = p[1] - campos[1], doz = p[2] - campos[2];
+      float len = sqrtf(dox * dox + doy * doy + doz * doz);
+      float x = dox / len, y = doy / len, z = doz / len;
+      const float* sh = shs + 3 * (long)M * i;
+      float* dsh = dL_dsh + 3 * (long)M * i;
+      float dRGB[3];
+      for (int ch = 0; ch < 3; ch++)
+        dRGB[ch] = dL_dcolor[3 * (long)i + ch] * (s->clamped[3 * (long)i + ch] ? 0.0f : 1.0f);
+      float ddir[3] = {0, 0, 0};
+      for (int ch = 0; ch < 3; ch++) {
+        #define SH(k) sh[3 * (k) + ch]
+        #define DSH(k) dsh[3 * (k) + ch]
+        float g = dRGB[ch];
+        float dx_ = 0, dy_ = 0, dz_ = 0;
+        DSH(0) = SH_C0 * g;
+        if (D > 0) {
+          DSH(1) = -SH_C1 * y * g; DSH(2) = SH_C1 * z * g; DSH(3) = -SH_C1 * x * g;
+          dx_ = -SH_C1 * SH(3); dy_ = -SH_C1 * SH(1); dz_ = SH_C1 * SH(2);
+          if (D > 1) {
+            float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+            DSH(4) = SH_C2[0] * xy * g; DSH(5) = SH_C2[1] * yz * g;
+            DSH(6) = SH_C2[2] * (2.f * zz - xx - yy) * g;
+            DSH(7) = SH_C2[3] * xz * g; DSH(8) = SH_C2[4] * (xx - yy) * g;
+            dx_ += SH_C2[0] * y * SH(4) + SH_C2[2] * 2.f * -x * SH(6) + SH_C2[3] * z * SH(7) + SH_C2[4] * 2.f * x * SH(8);
+            dy_ += SH_C2[0] * x * SH(4) + SH_C2[1] * z * SH(5) + SH_C2[2] * 2.f * -y * SH(6) + SH_C2[4] * 2.f * -y * SH(8);
+            dz_ += SH_C2[1] * y * SH(5) + SH_C2[2] * 2.f * 2.f * z * SH(6) + SH_C2[3] * x * SH(7);
+            if (D > 2) {
+              DSH(9) = SH_C3[0] * y * (3.f * xx - yy) * g;
+              DSH(10) = SH_C3[1] * xy * z * g;
+              DSH(11) = SH_C3[2] * y * (4.f * zz - xx - yy) * g;
+              DSH(12) = SH_C3[3] * z * (2.f * zz - 3.f * xx - 3.f * yy) * g;
+              DSH(13) = SH_C3[4] * x * (4.f * zz - xx - yy) * g;
+              DSH(14) = SH_C3[5] * z * (xx - yy) * g;
+              DSH(15) = SH_C3[6] * x * (xx - 3.f * yy) * g;
+              dx_ += SH_C3[0] * SH(9) * 3.f * 2.f * xy + SH_C3[1] * SH(10) * yz +
+                     SH_C3[2] * SH(11) * -2.f * xy + SH_C3[3] * SH(12) * -3.f * 2.f * xz +
+                     SH_C3[4] * SH(13) * (-3.f * xx + 4.f * zz - yy) +
+                     SH_C3[5] * SH(14) * 2.f * xz + SH_C3[6] * SH(15) * 3.f * (xx - yy);
+              dy_ += SH_C3[0] * SH(9) * 3.f * (xx - yy) + SH_C3[1] * SH(10) * xz +
+                     SH_C3[2] * SH(11) * (-3.f * yy + 4.f * zz - xx) +
+                     SH_C3[3] * SH(12) * -3.f * 2.f * yz + SH_C3[4] * SH(13) * -2.f * xy +
+                     SH_C3[5] * SH(14) * -2.f * yz + SH_C3[6] * SH(15) * -3.f * 2.f * xy;
+              dz_ += SH_C3[1] * SH(10) * xy + SH_C3[2] * SH(11) * 4.f * 2.f * yz +
+                     SH_C3[3] * SH(12) * 3.f * (2.f * zz - xx - yy) +
+                     SH_C3[4] * SH(13) * 4.f * 2.f * xz + SH_C3[5] * SH(14) * (xx - yy);
+            }
+          }
+        }
+        #undef SH
+        #undef DSH
+        ddir[0] += dx_ * g; ddir[1] += dy_ * g; ddir[2] += dz_ * g;
+      }
+      /* auxiliary.h:107-117 dnormvdv */
+      float sum2 = dox * dox + doy * doy + doz * doz;
+      float inv32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+      dm[0] += ((sum2 - dox * dox) * ddir[0] - doy * dox * ddir[1] - doz * dox * ddir[2]) * inv32;
+      dm[1] += (-dox * doy * ddir[0] + (sum2 - doy * doy) * ddir[1] - doz * doy * ddir[2]) * inv32;
+      dm[2] += (-dox * doz * ddir[0] - doy * doz * ddir[1] + (sum2 - doz * doz) * ddir[2]) * inv32;
+    }
+    dL_dmean3D[3 * (long)i] = dm[0]; dL_dmean3D[3 * (long)i + 1] = dm[1]; dL_dmean3D[3 * (long)i + 2] = dm[2];
+
+    /* backward.cu:278-341 computeCov3D backward; Rg[c][r] = glm column c, row r */
+    if (scales) {
+      const float* q = rotations + 4 * (long)i;
+      float r = q[0], x = q[1], y = q[2], z = q[3];
+      float Rg[3][3] = {
+        {1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+        {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+        {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+      float sv[3] = {scale_modifier * scales[3 * (long)i], scale_modifier * scales[3 * (long)i + 1],
+                     scale_modifier * scales[3 * (long)i + 2]};
+      float Sg[3][3] = {{dcov[0], 0.5f * dcov[1], 0.5f * dcov[2]},
+                        {0.5f * dcov[1], dcov[3], 0.5f * dcov[4]},
+                        {0.5f * dcov[2], 0.5f * dcov[4], dcov[5]}};
+      float dMt[3][3]; /* dMt[a][b] = dL_dM[b][a] = 2 * sum_k M[k][a] * Sg[b][k], M[k][a] = sv[a]*Rg[k][a] */
+      for (int a_ = 0; a_ < 3; a_++)
+        for (int b_ = 0; b_ < 3; b_++) {
+          float acc_ = 0;
+          for (int k = 0; k < 3; k++) acc_ += (sv[a_] * Rg[k][a_]) * Sg[b_][k];
+          dMt[a_][b_] = 2.0f * acc_;
+        }
+      for (int a_ = 0; a_ < 3; a_++) {
+        /* dot(Rt[a], dMt[a]) with Rt[a][b] = Rg[b][a] */
+        dL_dscale[3 * (long)i + a_] = Rg[0][a_] * dMt[a_][0] + Rg[1][a_] * dMt[a_][1] + Rg[2][a_] * dMt[a_][2];
+        for (int b_ = 0; b_ < 3; b_++) dMt[a_][b_] *= sv[a_];
+      }
+      float* dq = dL_drot + 4 * (long)i;
+      dq[0] = 2 * z * (dMt[0][1] - dMt[1][0]) + 2 * y * (dMt[2][0] - dMt[0][2]) + 2 * x * (dMt[1][2] - dMt[2][1]);
+      dq[1] = 2 * y * (dMt[1][0] + dMt[0][1]) + 2 * z * (dMt[2][0] + dMt[0][2]) + 2 * r * (dMt[1][2] - dMt[2][1]) - 4 * x * (dMt[2][2] + dMt[1][1]);
+      dq[2] = 2 * x * (dMt[1][0] + dMt[0][1]) + 2 * r * (dMt[2][0] - dMt[0][2]) + 2 * z * (dMt[1][2] + dMt[2][1]) - 4 * y * (dMt[2][2] + dMt[0][0]);
+      dq[3] = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) - 4 * z * (dMt[1][1] + dMt[0][0]);
+    }
+  }
+}
+
+/* DGR/cuda_rasterizer/rasterizer_impl.cu:54-66 checkFrustum / markVisible */
+void orc_mark_visible(int P, const float* means3D, const float* view, const float* proj,
+                      unsigned char* present) {
+  (void)proj;
+  for (int i = 0; i < P; i++) {
+    const float* p = means3D + 3 * (long)i;
+    float vz = xf_row(view, 2, p[0], p[1], p[2]);
+    present[i] = !(vz <= 0.2f);
+  }
+}
+
+int orc_num_threads(void) {
+#ifdef _OPENMP
+  return omp_get_max_threads();
+#else
+  return 1;
+#endif
+}
