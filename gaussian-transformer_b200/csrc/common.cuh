@@ -1,0 +1,190 @@
+// csrc/common.cuh -- shared constants, scratch layout and small device helpers
+// for libgsrast (B200 / sm_100a).  Own code; the reference
+// (DGR = /root/reference/submodules/diff-gaussian-rasterization) is cited only
+// for the behaviour each piece has to reproduce.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace gsr {
+
+// DGR/cuda_rasterizer/config.h:15-17 -- tile ids / ranges must be bit-exact, so
+// the tile stays 16x16 and there are 3 colour channels.
+constexpr int TILE = 16;
+constexpr int TILE_PIX = TILE * TILE;
+constexpr int NCH = 3;
+
+// DGR/cuda_rasterizer/auxiliary.h:22-39
+__device__ constexpr float SH_C0 = 0.28209479177387814f;
+__device__ constexpr float SH_C1 = 0.4886025119029199f;
+__device__ constexpr float SH_C2_0 = 1.0925484305920792f;
+__device__ constexpr float SH_C2_1 = -1.0925484305920792f;
+__device__ constexpr float SH_C2_2 = 0.31539156525252005f;
+__device__ constexpr float SH_C2_3 = -1.0925484305920792f;
+__device__ constexpr float SH_C2_4 = 0.5462742152960396f;
+__device__ constexpr float SH_C3_0 = -0.5900435899266435f;
+__device__ constexpr float SH_C3_1 = 2.890611442640554f;
+__device__ constexpr float SH_C3_2 = -0.4570457994644658f;
+__device__ constexpr float SH_C3_3 = 0.3731763325901154f;
+__device__ constexpr float SH_C3_4 = -0.4570457994644658f;
+__device__ constexpr float SH_C3_5 = 1.445305721320277f;
+__device__ constexpr float SH_C3_6 = -0.5900435899266435f;
+
+constexpr size_t ALIGN = 256;
+__host__ __device__ inline size_t align_up(size_t v) { return (v + ALIGN - 1) & ~(ALIGN - 1); }
+
+// ---------------------------------------------------------------- scratch layout
+// geom  (per Gaussian, written by preprocess_fwd, read by scatter / render / bwd)
+//   g0 float4[P]  mean2D.x, mean2D.y, depth, radius (int bits)
+//   g1 float4[P]  conic.x, conic.y, conic.z, opacity
+//   g2 float4[P]  r, g, b, flags (bits 0..2 = clamped r/g/b, bits 3.. = tiles_touched)
+// image
+//   final_T f32[N], n_contrib u32[N], ranges uint2[T], tile_count u32[T],
+//   tile_cursor u32[T], big_tiles u32[T] (ids of tiles whose list does not fit
+//   the small sort kernel), ctrl u32[64] (counters / flags)
+// binning
+//   keys u64[R] (depth bits << 32 | gaussian id, bucketed by tile, unsorted),
+//   point_list u32[R] (sorted gaussian ids)
+// bwd
+//   accA float4[P] dL_dcolor.rgb, dL_dopacity ; accB float4[P] dL_dmean2D.xy,
+//   dL_dconic.xx, .xy ; accC float[P] dL_dconic.yy
+struct GeomView {
+  float4* g0;
+  float4* g1;
+  float4* g2;
+};
+struct ImageView {
+  float* final_T;
+  uint32_t* n_contrib;
+  uint2* ranges;
+  uint32_t* tile_count;
+  uint32_t* tile_cursor;
+  uint32_t* big_tiles;
+  uint32_t* ctrl;
+};
+struct BinView {
+  unsigned long long* keys;
+  uint32_t* point_list;
+};
+struct BwdView {
+  float4* accA;
+  float4* accB;
+  float* accC;
+};
+
+// ctrl[] slots
+enum { CTRL_FLAGS = 0, CTRL_NBIG = 1, CTRL_NHUGE = 2, CTRL_R_LO = 4, CTRL_R_HI = 5, CTRL_WORDS = 64 };
+
+inline size_t geom_bytes(size_t P) { return 3 * align_up(16 * P) + ALIGN; }
+inline GeomView geom_view(void* base, size_t P) {
+  char* p = (char*)base;
+  GeomView v;
+  v.g0 = (float4*)p; p += align_up(16 * P);
+  v.g1 = (float4*)p; p += align_up(16 * P);
+  v.g2 = (float4*)p;
+  return v;
+}
+inline size_t image_bytes(size_t N, size_t T) {
+  return 2 * align_up(4 * N) + align_up(8 * T) + 3 * align_up(4 * T) + align_up(4 * CTRL_WORDS) + ALIGN;
+}
+inline ImageView image_view(void* base, size_t N, size_t T) {
+  char* p = (char*)base;
+  ImageView v;
+  v.final_T = (float*)p; p += align_up(4 * N);
+  v.n_contrib = (uint32_t*)p; p += align_up(4 * N);
+  v.ranges = (uint2*)p; p += align_up(8 * T);
+  v.tile_count = (uint32_t*)p; p += align_up(4 * T);
+  v.tile_cursor = (uint32_t*)p; p += align_up(4 * T);
+  v.big_tiles = (uint32_t*)p; p += align_up(4 * T);
+  v.ctrl = (uint32_t*)p;
+  return v;
+}
+inline size_t bin_bytes(size_t R) { return align_up(8 * R) + align_up(4 * R) + ALIGN; }
+inline BinView bin_view(void* base, size_t R) {
+  char* p = (char*)base;
+  BinView v;
+  v.keys = (unsigned long long*)p; p += align_up(8 * R);
+  v.point_list = (uint32_t*)p;
+  return v;
+}
+inline size_t bwd_bytes(size_t P) { return 2 * align_up(16 * P) + align_up(4 * P) + ALIGN; }
+inline BwdView bwd_view(void* base, size_t P) {
+  char* p = (char*)base;
+  BwdView v;
+  v.accA = (float4*)p; p += align_up(16 * P);
+  v.accB = (float4*)p; p += align_up(16 * P);
+  v.accC = (float*)p;
+  return v;
+}
+
+// Camera / raster constants handed to kernels by value.
+struct Cam {
+  const float* view;  // 16 floats, column-major
+  const float* proj;  // 16 floats
+  const float* campos;
+  float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
+  int W, H, gx, gy;
+};
+
+// ---------------------------------------------------------------- device helpers
+// m[r]*x + m[4+r]*y + m[8+r]*z + m[12+r] with the rounding points of the
+// reference's compiled transformPoint4x3/4x4 (DGR/cuda_rasterizer/auxiliary.h:58-77;
+// SASS: FADD(FFMA(z,m8,FFMA(x,m0,FMUL(y,m4))),m12)).  Explicit intrinsics so the
+// compiler can neither contract nor re-associate.
+__device__ __forceinline__ float xf_row(const float* __restrict__ m, int r, float x, float y, float z) {
+  float t = __fmul_rn(y, m[4 + r]);
+  t = __fmaf_rn(x, m[r], t);
+  t = __fmaf_rn(z, m[8 + r], t);
+  return __fadd_rn(t, m[12 + r]);
+}
+
+// a0*b0 + a1*b1 + a2*b2 as the reference's mat3 products compile:
+// FFMA(a2,b2,FFMA(a0,b0,FMUL(a1,b1))).
+__device__ __forceinline__ float dot3c(float a0, float b0, float a1, float b1, float a2, float b2) {
+  return __fmaf_rn(a2, b2, __fmaf_rn(a0, b0, __fmul_rn(a1, b1)));
+}
+
+// DGR/cuda_rasterizer/auxiliary.h:41-44 ndc2Pix, evaluated in FP64 like the
+// reference (DFMA((v+1), S, -1) * 0.5, then rounded to float).
+__device__ __forceinline__ float ndc2pix(float v, int S) {
+  double t = __fma_rn(__dadd_rn((double)v, 1.0), (double)S, -1.0);
+  return __double2float_rn(__dmul_rn(t, 0.5));
+}
+
+// DGR/cuda_rasterizer/auxiliary.h:46-56 getRect (C truncation = F2I.TRUNC,
+// saturating, NaN -> 0).
+__device__ __forceinline__ void get_rect(float px, float py, int radius, int gx, int gy,
+                                         int& minx, int& miny, int& maxx, int& maxy) {
+  float r = (float)radius;
+  minx = min(gx, max(0, __float2int_rz(__fmul_rn(__fsub_rn(px, r), 0.0625f))));
+  miny = min(gy, max(0, __float2int_rz(__fmul_rn(__fsub_rn(py, r), 0.0625f))));
+  maxx = min(gx, max(0, __float2int_rz(__fmul_rn(__fsub_rn(__fadd_rn(__fadd_rn(px, r), 16.0f), 1.0f), 0.0625f))));
+  maxy = min(gy, max(0, __float2int_rz(__fmul_rn(__fsub_rn(__fadd_rn(__fadd_rn(py, r), 16.0f), 1.0f), 0.0625f))));
+}
+
+// Gaussian exponent at pixel offset (dx,dy) with the reference's rounding
+// (DGR/cuda_rasterizer/forward.cu:337-339; SASS:
+// FFMA(FFMA(dx, dx*A, dy*(dy*C)), -0.5, -(dy*(dx*B)))).
+__device__ __forceinline__ float gauss_power(float dx, float dy, float A, float B, float C) {
+  float t1 = __fmul_rn(dy, __fmul_rn(dy, C));
+  float s = __fmaf_rn(dx, __fmul_rn(dx, A), t1);
+  float v = __fmul_rn(dy, __fmul_rn(dx, B));
+  return __fmaf_rn(s, -0.5f, -v);
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+  v += __shfl_xor_sync(0xffffffffu, v, 16);
+  v += __shfl_xor_sync(0xffffffffu, v, 8);
+  v += __shfl_xor_sync(0xffffffffu, v, 4);
+  v += __shfl_xor_sync(0xffffffffu, v, 2);
+  v += __shfl_xor_sync(0xffffffffu, v, 1);
+  return v;
+}
+
+// Vector float atomics (sm_90+): one RED for four consecutive floats.
+__device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+               : "memory");
+}
+
+}  // namespace gsr

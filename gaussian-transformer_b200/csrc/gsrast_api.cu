@@ -1,0 +1,279 @@
+// csrc/gsrast_api.cu -- the C ABI of libgsrast.so (see include/gsrast.h) and the
+// host-side orchestration of the kernels.  Stateless: no globals besides a
+// thread-local error string; no device allocation.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/gsrast.h"
+#include "binning.cuh"
+#include "common.cuh"
+#include "preprocess_bwd.cuh"
+#include "preprocess_fwd.cuh"
+#include "render_bwd.cuh"
+#include "render_fwd.cuh"
+
+using namespace gsr;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+  g_err = msg;
+  return code;
+}
+
+int cuda_fail(cudaError_t e, const char* where) {
+  return fail(GSR_ERR_CUDA, std::string(where) + ": " + cudaGetErrorString(e));
+}
+
+#define GSR_CUDA(call, where)                         \
+  do {                                                \
+    cudaError_t e__ = (call);                         \
+    if (e__ != cudaSuccess) return cuda_fail(e__, where); \
+  } while (0)
+
+// After a launch: always catch launch-configuration errors; with debug, also
+// synchronise so that a faulting stage is named (the reference's CHECK_CUDA,
+// DGR/cuda_rasterizer/auxiliary.h:166-173).
+#define GSR_STAGE(name, debug, stream)                                  \
+  do {                                                                  \
+    cudaError_t e__ = cudaGetLastError();                               \
+    if (e__ != cudaSuccess) return cuda_fail(e__, name);                \
+    if (debug) {                                                        \
+      e__ = cudaStreamSynchronize(stream);                              \
+      if (e__ != cudaSuccess) return cuda_fail(e__, name);              \
+    }                                                                   \
+  } while (0)
+
+bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+int check_inputs(const gsr_inputs* in) {
+  if (!in) return fail(GSR_ERR_INVALID, "gsr_inputs is NULL");
+  if (in->P < 0 || in->W <= 0 || in->H <= 0) return fail(GSR_ERR_INVALID, "bad P/W/H");
+  if (in->P == 0) return GSR_OK;
+  if (!in->means3D) return fail(GSR_ERR_INVALID, "means3D must have dimensions (num_points, 3)");
+  if (!in->opacities || !in->viewmatrix || !in->projmatrix || !in->bg)
+    return fail(GSR_ERR_INVALID, "opacities / viewmatrix / projmatrix / bg must not be NULL");
+  if (!in->colors_precomp) {
+    // DGR/cuda_rasterizer/rasterizer_impl.cu:242-245 has the same requirement for
+    // NUM_CHANNELS != 3; with 3 channels SHs are needed instead.
+    if (!in->sh || in->M <= 0) return fail(GSR_ERR_INVALID, "either sh (M > 0) or colors_precomp is required");
+    if (in->D < 0 || in->D > 3 || (in->D + 1) * (in->D + 1) > in->M)
+      return fail(GSR_ERR_INVALID, "sh degree does not fit the number of coefficients");
+    if (!in->campos) return fail(GSR_ERR_INVALID, "campos must not be NULL");
+  }
+  if (!in->cov3D_precomp) {
+    if (!in->scales || !in->rotations)
+      return fail(GSR_ERR_INVALID, "either scales+rotations or cov3D_precomp is required");
+    if (!aligned16(in->rotations)) return fail(GSR_ERR_INVALID, "rotations must be 16-byte aligned");
+  }
+  return GSR_OK;
+}
+
+Cam make_cam(const gsr_inputs* in) {
+  Cam c;
+  c.view = in->viewmatrix;
+  c.proj = in->projmatrix;
+  c.campos = in->campos;
+  c.tanfovx = in->tanfovx;
+  c.tanfovy = in->tanfovy;
+  // DGR/cuda_rasterizer/rasterizer_impl.cu:222-223
+  c.focal_y = in->H / (2.0f * in->tanfovy);
+  c.focal_x = in->W / (2.0f * in->tanfovx);
+  c.scale_modifier = in->scale_modifier;
+  c.W = in->W;
+  c.H = in->H;
+  c.gx = (in->W + TILE - 1) / TILE;
+  c.gy = (in->H + TILE - 1) / TILE;
+  return c;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gsr_version(void) { return 100; }
+int gsr_compiled_arch(void) { return 100; }
+const char* gsr_last_error(void) { return g_err.c_str(); }
+
+int gsr_scratch_bytes(int32_t P, int64_t R, int32_t W, int32_t H, size_t* geom, size_t* binning, size_t* image,
+                      size_t* bwd) {
+  if (P < 0 || R < 0 || W <= 0 || H <= 0) return fail(GSR_ERR_INVALID, "gsr_scratch_bytes: bad sizes");
+  const size_t N = (size_t)W * H;
+  const size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+  if (geom) *geom = geom_bytes((size_t)P);
+  if (binning) *binning = bin_bytes((size_t)R);
+  if (image) *image = image_bytes(N, T);
+  if (bwd) *bwd = bwd_bytes((size_t)P);
+  return GSR_OK;
+}
+
+int gsr_get_views(int32_t P, int64_t R, int32_t W, int32_t H, const void* geom, const void* binning,
+                  const void* image, gsr_views* out) {
+  if (!out) return fail(GSR_ERR_INVALID, "gsr_get_views: out is NULL");
+  memset(out, 0, sizeof(*out));
+  const size_t N = (size_t)W * H;
+  const size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
+  if (geom) {
+    GeomView g = geom_view(const_cast<void*>(geom), (size_t)P);
+    out->xy_depth_radius = (const float*)g.g0;
+    out->conic_opacity = (const float*)g.g1;
+    out->rgb_flags = (const float*)g.g2;
+  }
+  if (image) {
+    ImageView im = image_view(const_cast<void*>(image), N, T);
+    out->final_T = im.final_T;
+    out->n_contrib = im.n_contrib;
+    out->ranges = (const uint32_t*)im.ranges;
+    out->tile_count = im.tile_count;
+  }
+  if (binning) {
+    BinView b = bin_view(const_cast<void*>(binning), (size_t)R);
+    out->point_list = b.point_list;
+  }
+  return GSR_OK;
+}
+
+int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     uint8_t* present, void* stream_) {
+  (void)projmatrix;
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0) return fail(GSR_ERR_INVALID, "gsr_mark_visible: P < 0");
+  if (P == 0) return GSR_OK;
+  if (!means3D || !viewmatrix || !present) return fail(GSR_ERR_INVALID, "gsr_mark_visible: NULL pointer");
+  mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, viewmatrix, present);
+  GSR_STAGE("mark_visible", 0, stream);
+  return GSR_OK;
+}
+
+int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radii, int64_t* host_result,
+                    void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (int rc = check_inputs(in)) return rc;
+  if (!host_result) return fail(GSR_ERR_INVALID, "host_result is NULL");
+  if (in->P == 0) {
+    host_result[0] = 0;
+    host_result[1] = 0;
+    return GSR_OK;
+  }
+  if (!geom || !image || !radii) return fail(GSR_ERR_INVALID, "geom / image / radii must not be NULL");
+  const Cam cam = make_cam(in);
+  const size_t N = (size_t)in->W * in->H, T = (size_t)cam.gx * cam.gy;
+  GeomView g = geom_view(geom, (size_t)in->P);
+  ImageView im = image_view(image, N, T);
+  // tile_count[T] and ctrl are zeroed; tile_cursor / big_tiles are written by the scan
+  GSR_CUDA(cudaMemsetAsync(im.tile_count, 0, 4 * T, stream), "memset tile_count");
+  GSR_CUDA(cudaMemsetAsync(im.ctrl, 0, 4 * CTRL_WORDS, stream), "memset ctrl");
+  const int K = (in->D + 1) * (in->D + 1);
+  const bool vec_sh = in->sh && !in->colors_precomp && ((K * 3) % 4 == 0) && ((in->M * 12) % 16 == 0) &&
+                      aligned16(in->sh);
+  const int blocks = (in->P + 255) / 256;
+  if (vec_sh)
+    preprocess_fwd_kernel<true><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
+                                                            in->rotations, in->opacities, in->sh,
+                                                            in->colors_precomp, in->cov3D_precomp, cam,
+                                                            in->prefiltered, radii, g, im.tile_count, im.ctrl);
+  else
+    preprocess_fwd_kernel<false><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
+                                                             in->rotations, in->opacities, in->sh,
+                                                             in->colors_precomp, in->cov3D_precomp, cam,
+                                                             in->prefiltered, radii, g, im.tile_count, im.ctrl);
+  GSR_STAGE("preprocess_fwd", in->debug, stream);
+  tile_scan_kernel<<<1, 1024, 0, stream>>>((int)T, im.tile_count, im.ranges, im.tile_cursor, im.big_tiles, im.ctrl);
+  GSR_STAGE("tile_scan", in->debug, stream);
+  // ctrl[CTRL_R_LO..HI] -> host_result[0] (little endian int64), flags -> [1]
+  GSR_CUDA(cudaMemcpyAsync(&host_result[0], im.ctrl + CTRL_R_LO, 8, cudaMemcpyDeviceToHost, stream), "copy R");
+  GSR_CUDA(cudaMemcpyAsync(&host_result[1], im.ctrl + CTRL_FLAGS, 4, cudaMemcpyDeviceToHost, stream), "copy flags");
+  return GSR_OK;
+}
+
+int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void* image, int64_t R,
+                     float* out_color, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (int rc = check_inputs(in)) return rc;
+  if (!out_color) return fail(GSR_ERR_INVALID, "out_color is NULL");
+  if (R < 0) return fail(GSR_ERR_INVALID, "R < 0");
+  if (R > 0x7fffffffLL)
+    return fail(GSR_ERR_OVERFLOW, "num_rendered exceeds 2^31-1 (the reference's int would overflow)");
+  if (in->P == 0) {
+    // DGR/rasterize_points.cu:66,80-114: with no Gaussians the image stays 0 (not bg)
+    GSR_CUDA(cudaMemsetAsync(out_color, 0, sizeof(float) * NCH * (size_t)in->W * in->H, stream), "memset out");
+    return GSR_OK;
+  }
+  if (!geom || !image || (R > 0 && !binning)) return fail(GSR_ERR_INVALID, "scratch buffer is NULL");
+  const Cam cam = make_cam(in);
+  const size_t N = (size_t)in->W * in->H, T = (size_t)cam.gx * cam.gy;
+  GeomView g = geom_view(const_cast<void*>(geom), (size_t)in->P);
+  ImageView im = image_view(image, N, T);
+  BinView b = bin_view(binning, (size_t)R);
+  if (R > 0) {
+    scatter_instances_kernel<<<(in->P + 255) / 256, 256, 0, stream>>>(in->P, g.g0, cam.gx, cam.gy, im.ranges,
+                                                                     im.tile_cursor, b.keys);
+    GSR_STAGE("scatter_instances", in->debug, stream);
+    tile_sort_small_kernel<<<(unsigned)T, 256, 0, stream>>>(im.ranges, b.keys, b.point_list);
+    GSR_STAGE("tile_sort_small", in->debug, stream);
+    const int big_smem = SORT_BIG_CAP * 8;
+    // per-device function attribute; a few hundred ns, so simply applied on every call (no global state)
+    GSR_CUDA(cudaFuncSetAttribute(tile_sort_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, big_smem),
+             "tile_sort_big smem attribute");
+    tile_sort_big_kernel<<<148, 1024, big_smem, stream>>>(im.big_tiles, im.ctrl, im.ranges, b.keys, b.point_list);
+    GSR_STAGE("tile_sort_big", in->debug, stream);
+  }
+  dim3 grid(cam.gx, cam.gy), block(TILE, TILE);
+  render_fwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, g.g0, g.g1, g.g2,
+                                                in->colors_precomp, in->bg, im.final_T, im.n_contrib, out_color);
+  GSR_STAGE("render_fwd", in->debug, stream);
+  return GSR_OK;
+}
+
+int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, const void* binning,
+                 const void* image, int64_t R, const float* dL_dpix, float* dL_dmeans3D, float* dL_dmeans2D,
+                 float* dL_dsh, float* dL_dcolors, float* dL_dopacity, float* dL_dscales, float* dL_drotations,
+                 float* dL_dcov3D, float* dL_dconic, void* bwd_scratch, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (int rc = check_inputs(in)) return rc;
+  if (in->P == 0) return GSR_OK;
+  if (!radii || !geom || !image || !dL_dpix || !bwd_scratch || (R > 0 && !binning))
+    return fail(GSR_ERR_INVALID, "gsr_backward: NULL buffer");
+  if (!dL_dmeans3D || !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dscales || !dL_drotations ||
+      !dL_dcov3D || !dL_dconic)
+    return fail(GSR_ERR_INVALID, "gsr_backward: NULL gradient output");
+  if (in->sh && in->M > 0 && !dL_dsh) return fail(GSR_ERR_INVALID, "gsr_backward: dL_dsh is NULL");
+  if (!aligned16(dL_drotations) || !aligned16(dL_dconic))
+    return fail(GSR_ERR_INVALID, "dL_drotations / dL_dconic must be 16-byte aligned");
+  const Cam cam = make_cam(in);
+  const size_t N = (size_t)in->W * in->H, T = (size_t)cam.gx * cam.gy;
+  GeomView g = geom_view(const_cast<void*>(geom), (size_t)in->P);
+  ImageView im = image_view(const_cast<void*>(image), N, T);
+  BinView b = bin_view(const_cast<void*>(binning), (size_t)R);
+  BwdView bw = bwd_view(bwd_scratch, (size_t)in->P);
+  GSR_CUDA(cudaMemsetAsync(bwd_scratch, 0, bwd_bytes((size_t)in->P), stream), "memset bwd accumulators");
+  if (R > 0) {
+    dim3 grid(cam.gx, cam.gy), block(TILE, TILE);
+    render_bwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0, g.g1, g.g2,
+                                                  in->colors_precomp, im.final_T, im.n_contrib, dL_dpix, bw.accA,
+                                                  bw.accB, bw.accC);
+    GSR_STAGE("render_bwd", in->debug, stream);
+  }
+  BwdOut out;
+  out.dL_dmeans3D = dL_dmeans3D;
+  out.dL_dmeans2D = dL_dmeans2D;
+  out.dL_dsh = (in->M > 0) ? dL_dsh : nullptr;
+  out.dL_dcolors = dL_dcolors;
+  out.dL_dopacity = dL_dopacity;
+  out.dL_dscales = dL_dscales;
+  out.dL_drot = dL_drotations;
+  out.dL_dcov3D = dL_dcov3D;
+  out.dL_dconic = dL_dconic;
+  preprocess_bwd_kernel<<<(in->P + 255) / 256, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
+                                                                in->rotations, in->sh, in->cov3D_precomp, cam,
+                                                                radii, g.g2, bw.accA, bw.accB, bw.accC, out);
+  GSR_STAGE("preprocess_bwd", in->debug, stream);
+  return GSR_OK;
+}
+
+}  // extern "C"

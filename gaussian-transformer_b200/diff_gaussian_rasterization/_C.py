@@ -1,0 +1,150 @@
+"""`_C`-shaped shim over the C-ABI library.
+
+Same three entry points, argument order and return tuples as the reference's
+pybind module (DGR/ext.cpp:15-19, DGR/rasterize_points.h:18-67), so that
+snapshot_fw.dump / snapshot_bw.dump argument tuples replay unchanged.  All
+tensors are torch-owned; the library only sees raw device pointers
+(torch is plumbing here: memory, streams).
+"""
+import ctypes
+import threading
+
+import torch
+
+from . import _lib
+
+_tls = threading.local()
+
+
+def _host_result():
+    """Pinned int64[2] per thread: [num_rendered, flags] written by gsr_forward_pre."""
+    buf = getattr(_tls, "host_result", None)
+    if buf is None:
+        buf = torch.zeros(2, dtype=torch.int64).pin_memory()
+        _tls.host_result = buf
+    return buf
+
+
+def _f32(t, device):
+    """Dense fp32 CUDA view of `t` (DGR/rasterize_points.cu:94-111 .contiguous()), or None when absent."""
+    if t is None or t.numel() == 0:
+        return None
+    if t.device != device:
+        raise RuntimeError(f"gsrast: tensor on {t.device}, expected {device} (there is no CPU path)")
+    if t.dtype != torch.float32:
+        t = t.float()
+    t = t.contiguous()
+    if t.data_ptr() % 16:
+        t = t.clone()
+    return t
+
+
+def _ptr(t):
+    return 0 if t is None else t.data_ptr()
+
+
+def _inputs(P, D, M, W, H, tanfovx, tanfovy, scale_modifier, prefiltered, debug, bg, means3D, sh, colors,
+            opacity, scales, rotations, cov3D, view, proj, campos):
+    a = _lib.gsr_inputs()
+    a.P, a.D, a.M, a.W, a.H = P, D, M, W, H
+    a.tanfovx, a.tanfovy, a.scale_modifier = tanfovx, tanfovy, scale_modifier
+    a.prefiltered, a.debug = int(bool(prefiltered)), int(bool(debug))
+    a.bg, a.means3D, a.sh, a.colors_precomp = _ptr(bg), _ptr(means3D), _ptr(sh), _ptr(colors)
+    a.opacities, a.scales, a.rotations, a.cov3D_precomp = _ptr(opacity), _ptr(scales), _ptr(rotations), _ptr(cov3D)
+    a.viewmatrix, a.projmatrix, a.campos = _ptr(view), _ptr(proj), _ptr(campos)
+    return a
+
+
+def _check_means(means3D):
+    if means3D.ndim != 2 or means3D.size(1) != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")  # rasterize_points.cu:57-59
+    if not means3D.is_cuda:
+        raise RuntimeError("gsrast: means3D must be a CUDA tensor (there is no CPU path)")
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                        viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
+                        prefiltered, debug):
+    """-> (num_rendered, out_color (3,H,W), radii (P,) int32, geomBuffer, binningBuffer, imgBuffer)."""
+    _check_means(means3D)
+    dev = means3D.device
+    P, H, W = means3D.size(0), int(image_height), int(image_width)
+    u8 = dict(dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        if P == 0:  # rasterize_points.cu:66-67,80-114: image stays 0, buffers empty
+            return (0, torch.zeros(3, H, W, dtype=torch.float32, device=dev),
+                    torch.zeros(0, dtype=torch.int32, device=dev), torch.empty(0, **u8), torch.empty(0, **u8),
+                    torch.empty(0, **u8))
+        M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
+        t = [_f32(x, dev) for x in (background, means3D, sh, colors, opacity, scales, rotations, cov3D_precomp,
+                                    viewmatrix, projmatrix, campos)]
+        args = _inputs(P, int(degree), M, W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier), prefiltered,
+                       debug, *t)
+        gb, _, ib, _ = _lib.scratch_bytes(P, 0, W, H)
+        geom, image = torch.empty(gb, **u8), torch.empty(ib, **u8)
+        radii = torch.empty(P, dtype=torch.int32, device=dev)
+        out_color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
+        host = _host_result()
+        stream = torch.cuda.current_stream(dev)
+        _lib.check(_lib.lib.gsr_forward_pre(ctypes.byref(args), geom.data_ptr(), image.data_ptr(), radii.data_ptr(),
+                                            host.data_ptr(), stream.cuda_stream))
+        stream.synchronize()  # the one host round trip (rasterizer_impl.cu:281)
+        R, flags = int(host[0]), int(host[1])
+        if flags & 1:
+            raise RuntimeError("gsrast: point is filtered although prefiltered is set. This shouldn't happen!")
+        if R > 0x7FFFFFFF:
+            raise RuntimeError(f"gsrast: num_rendered = {R} does not fit a 32-bit int")
+        _, bb, _, _ = _lib.scratch_bytes(P, R, W, H)
+        binning = torch.empty(bb if R > 0 else 0, **u8)
+        _lib.check(_lib.lib.gsr_forward_post(ctypes.byref(args), geom.data_ptr(), _ptr(binning) if R > 0 else 0,
+                                             image.data_ptr(), R, out_color.data_ptr(), stream.cuda_stream))
+    return R, out_color, radii, geom, binning, image
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                 cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh,
+                                 degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug):
+    """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+    _check_means(means3D)
+    dev = means3D.device
+    P = means3D.size(0)
+    H, W = dL_dout_color.size(1), dL_dout_color.size(2)
+    M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
+    f32 = dict(dtype=torch.float32, device=dev)
+    g = dict(means3D=torch.empty(P, 3, **f32), means2D=torch.empty(P, 3, **f32), sh=torch.empty(P, M, 3, **f32),
+             colors=torch.empty(P, 3, **f32), opacity=torch.empty(P, 1, **f32), scales=torch.empty(P, 3, **f32),
+             rot=torch.empty(P, 4, **f32), cov3D=torch.empty(P, 6, **f32), conic=torch.empty(P, 2, 2, **f32))
+    if P != 0:
+        with torch.cuda.device(dev):
+            t = [_f32(x, dev) for x in (background, means3D, sh, colors, None, scales, rotations, cov3D_precomp,
+                                        viewmatrix, projmatrix, campos)]
+            # opacities are not needed by backward (they live in geomBuffer); pass a valid pointer for the checker
+            t[4] = t[1]
+            args = _inputs(P, int(degree), M, W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier), False,
+                           debug, *t)
+            dpix = _f32(dL_dout_color, dev)
+            _, _, _, wb = _lib.scratch_bytes(P, int(R), W, H)
+            work = torch.empty(wb, dtype=torch.uint8, device=dev)
+            _lib.check(_lib.lib.gsr_backward(
+                ctypes.byref(args), radii.data_ptr(), geomBuffer.data_ptr(),
+                binningBuffer.data_ptr() if binningBuffer.numel() else 0, imageBuffer.data_ptr(), int(R),
+                dpix.data_ptr(), g["means3D"].data_ptr(), g["means2D"].data_ptr(), _ptr(g["sh"]) if M else 0,
+                g["colors"].data_ptr(), g["opacity"].data_ptr(), g["scales"].data_ptr(), g["rot"].data_ptr(),
+                g["cov3D"].data_ptr(), g["conic"].data_ptr(), work.data_ptr(),
+                torch.cuda.current_stream(dev).cuda_stream))
+    rasterize_gaussians_backward.last_dL_dconic = g["conic"]  # exposed for the parity tests only
+    return (g["means2D"], g["colors"], g["opacity"], g["means3D"], g["cov3D"], g["sh"], g["scales"], g["rot"])
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """bool (P,): view-space z > 0.2 (DGR/rasterize_points.cu:198-217)."""
+    _check_means(means3D)
+    dev = means3D.device
+    P = means3D.size(0)
+    present = torch.zeros(P, dtype=torch.bool, device=dev)
+    if P != 0:
+        with torch.cuda.device(dev):
+            m, v, p = _f32(means3D, dev), _f32(viewmatrix, dev), _f32(projmatrix, dev)
+            _lib.check(_lib.lib.gsr_mark_visible(P, m.data_ptr(), v.data_ptr(), p.data_ptr(), present.data_ptr(),
+                                                 torch.cuda.current_stream(dev).cuda_stream))
+    return present

@@ -1,0 +1,75 @@
+"""ctypes binding of libgsrast.so (include/gsrast.h).
+
+The product path has NO fallback: if the CUDA library is missing or fails to
+load, importing this module raises.  Nothing here imports the oracle.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libgsrast.so")
+
+
+class gsr_inputs(ctypes.Structure):
+    _fields_ = [
+        ("P", ctypes.c_int32), ("D", ctypes.c_int32), ("M", ctypes.c_int32),
+        ("W", ctypes.c_int32), ("H", ctypes.c_int32),
+        ("tanfovx", ctypes.c_float), ("tanfovy", ctypes.c_float), ("scale_modifier", ctypes.c_float),
+        ("prefiltered", ctypes.c_int32), ("debug", ctypes.c_int32),
+        ("bg", ctypes.c_void_p), ("means3D", ctypes.c_void_p), ("sh", ctypes.c_void_p),
+        ("colors_precomp", ctypes.c_void_p), ("opacities", ctypes.c_void_p), ("scales", ctypes.c_void_p),
+        ("rotations", ctypes.c_void_p), ("cov3D_precomp", ctypes.c_void_p), ("viewmatrix", ctypes.c_void_p),
+        ("projmatrix", ctypes.c_void_p), ("campos", ctypes.c_void_p),
+    ]
+
+
+class gsr_views(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_void_p) for n in (
+        "xy_depth_radius", "conic_opacity", "rgb_flags", "final_T", "n_contrib", "ranges", "tile_count",
+        "point_list")]
+
+
+# every symbol include/gsrast.h declares
+EXPORTS = (
+    "gsr_version", "gsr_compiled_arch", "gsr_last_error", "gsr_scratch_bytes", "gsr_forward_pre",
+    "gsr_forward_post", "gsr_backward", "gsr_mark_visible", "gsr_get_views",
+)
+
+
+def load(path=LIB_PATH):
+    if not os.path.exists(path):
+        raise ImportError(
+            f"libgsrast.so not found at {path}: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"or `make -C gaussian-transformer_b200/csrc` (there is no CPU fallback)")
+    lib = ctypes.CDLL(path)
+    vp, i32, i64 = ctypes.c_void_p, ctypes.c_int32, ctypes.c_int64
+    szp = ctypes.POINTER(ctypes.c_size_t)
+    inp = ctypes.POINTER(gsr_inputs)
+    lib.gsr_version.restype = ctypes.c_int
+    lib.gsr_compiled_arch.restype = ctypes.c_int
+    lib.gsr_last_error.restype = ctypes.c_char_p
+    lib.gsr_scratch_bytes.argtypes = [i32, i64, i32, i32, szp, szp, szp, szp]
+    lib.gsr_forward_pre.argtypes = [inp, vp, vp, vp, vp, vp]
+    lib.gsr_forward_post.argtypes = [inp, vp, vp, vp, i64, vp, vp]
+    lib.gsr_backward.argtypes = [inp, vp, vp, vp, vp, i64, vp] + [vp] * 9 + [vp, vp]
+    lib.gsr_mark_visible.argtypes = [i32, vp, vp, vp, vp, vp]
+    lib.gsr_get_views.argtypes = [i32, i64, i32, i32, vp, vp, vp, ctypes.POINTER(gsr_views)]
+    for name in ("gsr_scratch_bytes", "gsr_forward_pre", "gsr_forward_post", "gsr_backward", "gsr_mark_visible",
+                 "gsr_get_views"):
+        getattr(lib, name).restype = ctypes.c_int
+    return lib
+
+
+lib = load()
+
+
+def check(rc):
+    if rc != 0:
+        msg = lib.gsr_last_error()
+        raise RuntimeError("gsrast: " + (msg.decode() if msg else f"error {rc}"))
+
+
+def scratch_bytes(P, R, W, H):
+    g, b, i, w = (ctypes.c_size_t() for _ in range(4))
+    check(lib.gsr_scratch_bytes(P, R, W, H, ctypes.byref(g), ctypes.byref(b), ctypes.byref(i), ctypes.byref(w)))
+    return g.value, b.value, i.value, w.value

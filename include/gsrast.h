@@ -1,0 +1,166 @@
+/* include/gsrast.h -- C ABI of libgsrast.so, the B200-native (sm_100a)
+ * differentiable Gaussian rasterizer.
+ *
+ * This is the drop-in boundary for the one hot path of
+ * stu214634/gaussian-transformer: submodules/diff-gaussian-rasterization
+ * (abbreviated DGR).  Each entry point states the reference interface it
+ * replaces (file:line under /root/reference).  Plain pointers and sizes only:
+ * no torch / pybind / C++ types cross this boundary.
+ *
+ * Conventions
+ *   - every pointer named in gsr_inputs / the gradient arguments is a DEVICE
+ *     pointer (what tensor.data_ptr() returns); NULL means "absent", exactly
+ *     as an empty tensor does in the reference (DGR/cuda_rasterizer/forward.cu:205,241);
+ *   - all arrays are dense fp32 in the reference's layouts
+ *     (DGR/rasterize_points.cu:94-111): means3D (P,3), sh (P,M,3),
+ *     colors_precomp (P,3), opacities (P,1), scales (P,3), rotations (P,4),
+ *     cov3D_precomp (P,6), viewmatrix / projmatrix 16 floats read column-major
+ *     (DGR/cuda_rasterizer/auxiliary.h:58-77), campos 3, bg 3;
+ *   - the library never allocates or frees device memory and keeps no global
+ *     state: the caller owns outputs and the three scratch buffers (sized by
+ *     gsr_scratch_bytes), which carry everything backward needs -- the same
+ *     contract as the reference's geomBuffer / binningBuffer / imgBuffer
+ *     (DGR/rasterize_points.cu:27-33,73-78);
+ *   - `stream` is a cudaStream_t passed as void* (0 = legacy default stream);
+ *     all work is enqueued on it; calls are re-entrant across threads/devices;
+ *   - return value 0 = success; otherwise gsr_last_error() (thread-local)
+ *     describes the failure.  The Python wrapper raises RuntimeError, the
+ *     exception type the reference's callers catch
+ *     (train_stacked_transformer.py:392).
+ *
+ * Forward is two-phase because the per-instance scratch can only be sized once
+ * num_rendered is known -- the reference has the same host round trip
+ * (DGR/cuda_rasterizer/rasterizer_impl.cu:277-285).
+ */
+#ifndef GSRAST_H_
+#define GSRAST_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define GSR_API __attribute__((visibility("default")))
+#else
+#define GSR_API
+#endif
+
+#define GSR_OK 0
+#define GSR_ERR_INVALID 1  /* bad argument (shape, NULL, alignment) */
+#define GSR_ERR_CUDA 2     /* a CUDA call or kernel failed */
+#define GSR_ERR_OVERFLOW 3 /* num_rendered does not fit the reference's int */
+#define GSR_ERR_PREFILTERED 4 /* a Gaussian was culled although prefiltered=1 */
+
+/* Per-call arguments: the positional argument list of the reference's
+ * _C.rasterize_gaussians (DGR/rasterize_points.h:18-38) minus the tensors the
+ * library writes.  P = means3D.size(0); M = sh.size(1) (0 when sh is absent,
+ * DGR/rasterize_points.cu:83-87); D = active SH degree; W, H = image size. */
+typedef struct gsr_inputs {
+  int32_t P, D, M, W, H;
+  float tanfovx, tanfovy, scale_modifier;
+  int32_t prefiltered, debug;
+  const float* bg;
+  const float* means3D;
+  const float* sh;
+  const float* colors_precomp;
+  const float* opacities;
+  const float* scales;
+  const float* rotations;
+  const float* cov3D_precomp;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* campos;
+} gsr_inputs;
+
+/* Library version (major*10000 + minor*100 + patch) and the SM architecture the
+ * kernels were compiled for (100 = sm_100a). */
+GSR_API int gsr_version(void);
+GSR_API int gsr_compiled_arch(void);
+
+/* Thread-local description of the last non-zero return on this thread. */
+GSR_API const char* gsr_last_error(void);
+
+/* Scratch sizes in bytes.  Replaces the required<T>() size queries the
+ * reference runs inside its resize callbacks
+ * (DGR/cuda_rasterizer/rasterizer_impl.h:67-72, rasterizer_impl.cu:225-240,283).
+ * geom depends on P; image on W,H; binning on R (= num_rendered, pass 0 when
+ * not known yet); bwd on P (per-Gaussian accumulators of the backward pass).
+ * Any out pointer may be NULL.  All buffers must be 256-byte aligned. */
+GSR_API int gsr_scratch_bytes(int32_t P, int64_t R, int32_t W, int32_t H, size_t* geom,
+                      size_t* binning, size_t* image, size_t* bwd);
+
+/* Forward, phase 1: preprocess (EWA projection, cov3D/cov2D, SH -> RGB, radii,
+ * tile rectangles) + per-tile instance counts + tile ranges.
+ * Replaces FORWARD::preprocess and the InclusiveSum / D2H copy of
+ * CudaRasterizer::Rasterizer::forward (DGR/cuda_rasterizer/rasterizer_impl.cu:198-281,
+ * forward.cu:155-256).
+ *   radii        int32[P]  out (0 for culled Gaussians; fully written)
+ *   host_result  int64[2]  PINNED HOST memory, written asynchronously on
+ *                          `stream`: [0] = num_rendered, [1] = error flags
+ *                          (bit 0: prefiltered violation).  The caller must
+ *                          synchronise `stream` before reading it.
+ * P == 0 is legal: nothing is launched and host_result is zeroed on return. */
+GSR_API int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radii,
+                    int64_t* host_result, void* stream);
+
+/* Forward, phase 2: instance scatter into per-tile buckets, per-tile depth sort
+ * (order identical to the reference's stable 64-bit tile|depth radix sort),
+ * alpha compositing.  Replaces duplicateWithKeys, cub::DeviceRadixSort,
+ * identifyTileRanges and FORWARD::render
+ * (DGR/cuda_rasterizer/rasterizer_impl.cu:283-331, forward.cu:261-374).
+ *   R          num_rendered as read from host_result[0]
+ *   out_color  float[3*H*W] out, fully written (C + T*bg). */
+GSR_API int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning,
+                     void* image, int64_t R, float* out_color, void* stream);
+
+/* Backward.  Replaces CudaRasterizer::Rasterizer::backward
+ * (DGR/cuda_rasterizer/rasterizer_impl.cu:340-434; BACKWARD::render
+ * backward.cu:399-557, computeCov2DCUDA :144-274, preprocessCUDA :346-396) and
+ * the nine zero-filled gradient tensors of the torch glue
+ * (DGR/rasterize_points.cu:151-159): every non-NULL output is FULLY written
+ * (zeros where the reference leaves its zero-initialised tensors untouched),
+ * so the caller may pass uninitialised memory.
+ *   dL_dpix      float[3*H*W]  upstream gradient of out_color
+ *   dL_dmeans3D  float[P*3]    dL_dmeans2D float[P*3] (z = 0)
+ *   dL_dsh       float[P*M*3]  (NULL allowed when sh is absent)
+ *   dL_dcolors   float[P*3]    dL_dopacity float[P]
+ *   dL_dscales   float[P*3]    dL_drotations float[P*4]
+ *   dL_dcov3D    float[P*6]    dL_dconic float[P*4] ((P,2,2): xx, xy, -, yy)
+ *   bwd_scratch  gsr_scratch_bytes(...).bwd bytes. */
+GSR_API int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom,
+                 const void* binning, const void* image, int64_t R,
+                 const float* dL_dpix, float* dL_dmeans3D, float* dL_dmeans2D,
+                 float* dL_dsh, float* dL_dcolors, float* dL_dopacity,
+                 float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                 float* dL_dconic, void* bwd_scratch, void* stream);
+
+/* present[i] = (view-space z > 0.2).  Replaces Rasterizer::markVisible /
+ * checkFrustum (DGR/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153). */
+GSR_API int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, uint8_t* present, void* stream);
+
+/* Decoded views into the scratch buffers of a finished forward (device
+ * pointers into geom / image / binning) -- the counterpart of
+ * GeometryState / ImageState / BinningState::fromChunk
+ * (DGR/cuda_rasterizer/rasterizer_impl.cu:155-194), used by the parity tests
+ * for stage-by-stage comparison. */
+typedef struct gsr_views {
+  const float* xy_depth_radius; /* float4[P]: mean2D.x, .y, depth, radius (int bits) */
+  const float* conic_opacity;   /* float4[P] */
+  const float* rgb_flags;       /* float4[P]: r, g, b, (tiles_touched<<3 | clamped) bits */
+  const float* final_T;         /* float[N] */
+  const uint32_t* n_contrib;    /* uint32[N] */
+  const uint32_t* ranges;       /* uint2[T] */
+  const uint32_t* tile_count;   /* uint32[T] */
+  const uint32_t* point_list;   /* uint32[R] sorted Gaussian ids */
+} gsr_views;
+GSR_API int gsr_get_views(int32_t P, int64_t R, int32_t W, int32_t H, const void* geom,
+                  const void* binning, const void* image, gsr_views* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSRAST_H_ */

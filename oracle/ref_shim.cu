@@ -191,6 +191,12 @@ struct RefViews {
   const uint64_t* point_list_keys_unsorted;
 };
 
+// Device-to-device copy helper so that the tests can pull decoded views into
+// torch tensors without binding libcudart themselves.
+int ref_copy(void* dst, const void* src, size_t nbytes) {
+  return (int)cudaMemcpy(dst, src, nbytes, cudaMemcpyDeviceToDevice);
+}
+
 int ref_views(void* h, RefViews* v) {
   RefCtx* c = (RefCtx*)h;
   memset(v, 0, sizeof(*v));

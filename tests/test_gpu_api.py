@@ -1,0 +1,148 @@
+"""GPU tests of the Python surface (GaussianRasterizer / rasterize_gaussians / markVisible): every argument
+combination of DGR/diff_gaussian_rasterization/__init__.py:187-220, autograd wiring, edge cases."""
+import numpy as np
+import pytest
+import torch
+
+import cases
+import gsr_scenes as S
+from util import np_, rel_err, settings_from, to_device
+
+pytestmark = pytest.mark.gpu
+
+
+def _module(d, **kw):
+    from diff_gaussian_rasterization import GaussianRasterizer
+    return GaussianRasterizer(settings_from(d, **kw))
+
+
+def _leaf(t):
+    return t.clone().requires_grad_(True)
+
+
+def test_autograd_matches_reference(reference):
+    sc, _ = cases.case("s_deg3")
+    d = to_device(sc)
+    m3, sh, op, scl, rot = (_leaf(d[k]) for k in ("means3D", "sh", "opacities", "scales", "rotations"))
+    m2 = torch.zeros_like(m3, requires_grad=True)
+    color, radii = _module(d)(means3D=m3, means2D=m2, opacities=op, shs=sh, scales=scl, rotations=rot)
+    assert color.shape == (3, sc["H"], sc["W"]) and radii.dtype == torch.int32 and radii.shape == (sc["P"],)
+    dpix = torch.from_numpy(S.upstream_grad(sc["W"], sc["H"], 5)).cuda()
+    (color * dpix).sum().backward()
+    ref = reference.forward(d, internals=False)
+    g = reference.backward(dpix)
+    assert np.abs(np_(color) - np_(ref["color"])).max() <= 1e-5
+    for t, k in ((m3, "means3D"), (m2, "means2D"), (sh, "sh"), (op, "opacity"), (scl, "scales"), (rot, "rot")):
+        assert t.grad is not None and t.grad.shape == t.shape, k
+        assert rel_err(np_(t.grad), np_(g[k]).reshape(t.shape)) <= 1e-3, k
+    assert float(m2.grad[:, 2].abs().max()) == 0.0
+
+
+def test_colors_and_cov_paths():
+    sc, _ = cases.case("s_deg3")
+    d = to_device(sc)
+    P = sc["P"]
+    cols = _leaf(torch.rand(P, 3, device="cuda"))
+    cov = _leaf(torch.from_numpy(S.covariance_from_scale_rot(sc["scales"], sc["rotations"])).cuda())
+    m3, op = _leaf(d["means3D"]), _leaf(d["opacities"])
+    color, radii = _module(d)(means3D=m3, means2D=torch.zeros_like(m3), opacities=op, colors_precomp=cols,
+                              cov3D_precomp=cov)
+    color.sum().backward()
+    assert cols.grad.shape == (P, 3) and cov.grad.shape == (P, 6) and m3.grad.shape == (P, 3)
+    assert torch.isfinite(cols.grad).all() and float(cols.grad.abs().sum()) > 0 and float(cov.grad.abs().sum()) > 0
+
+
+def test_argument_validation():
+    sc, _ = cases.case("s_deg0_m1")
+    d = to_device(sc)
+    r = _module(d)
+    m3, op = d["means3D"], d["opacities"]
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        r(means3D=m3, means2D=m3, opacities=op, scales=d["scales"], rotations=d["rotations"])
+    with pytest.raises(Exception, match="excatly one of either SHs or precomputed colors"):
+        r(means3D=m3, means2D=m3, opacities=op, shs=d["sh"], colors_precomp=m3, scales=d["scales"],
+          rotations=d["rotations"])
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(means3D=m3, means2D=m3, opacities=op, shs=d["sh"], scales=d["scales"])
+    with pytest.raises(Exception, match="scale/rotation pair or precomputed 3D covariance"):
+        r(means3D=m3, means2D=m3, opacities=op, shs=d["sh"], scales=d["scales"], rotations=d["rotations"],
+          cov3D_precomp=torch.zeros(sc["P"], 6, device="cuda"))
+    with pytest.raises(RuntimeError, match=r"means3D must have dimensions \(num_points, 3\)"):
+        r(means3D=m3[:, :2], means2D=m3, opacities=op, shs=d["sh"], scales=d["scales"], rotations=d["rotations"])
+    with pytest.raises(RuntimeError):
+        r(means3D=m3.cpu(), means2D=m3, opacities=op, shs=d["sh"], scales=d["scales"], rotations=d["rotations"])
+
+
+def test_empty_input_gives_zero_image_not_bg():
+    sc, _ = cases.case("s_bg_yaw")
+    d = to_device(sc)
+    z = lambda *s: torch.zeros(*s, device="cuda")
+    color, radii = _module(d)(means3D=z(0, 3), means2D=z(0, 3), opacities=z(0, 1), shs=z(0, 16, 3), scales=z(0, 3),
+                              rotations=z(0, 4))
+    assert radii.numel() == 0 and float(color.abs().max()) == 0.0  # rasterize_points.cu:66,80-114
+
+
+def test_all_culled_is_background_and_zero_grads():
+    sc, _ = cases.case("all_culled")
+    sc["bg"] = np.array([0.2, 0.4, 0.6], np.float32)
+    d = to_device(sc)
+    m3 = _leaf(d["means3D"])
+    color, radii = _module(d)(means3D=m3, means2D=torch.zeros_like(m3), opacities=d["opacities"], shs=d["sh"],
+                              scales=d["scales"], rotations=d["rotations"])
+    assert int(radii.max()) == 0
+    assert torch.allclose(color, d["bg"].view(3, 1, 1).expand_as(color))
+    color.sum().backward()
+    assert float(m3.grad.abs().max()) == 0.0
+
+
+def test_strided_views_like_box_sort_consumers(reference):
+    """model/box_sort.py:17-27 hands the rasterizer column slices of one (P,26) tensor."""
+    sc, _ = cases.case("s_deg1_m4")
+    d = to_device(sc)
+    P = sc["P"]
+    flat = torch.cat([d["means3D"], d["scales"], d["rotations"], d["opacities"], d["sh"].reshape(P, 12)], 1)
+    flat = _leaf(flat)
+    m3, scl, rot, op, sh = flat[:, 0:3], flat[:, 3:6], flat[:, 6:10], flat[:, 10:11], flat[:, 11:23].reshape(P, 4, 3)
+    color, _ = _module(d)(means3D=m3, means2D=torch.zeros(P, 3, device="cuda"), opacities=op, shs=sh, scales=scl,
+                          rotations=rot)
+    ref = reference.forward(d, internals=False)
+    assert np.abs(np_(color) - np_(ref["color"])).max() <= 1e-5
+    color.sum().backward()
+    assert flat.grad.shape == (P, 23) and torch.isfinite(flat.grad).all()
+
+
+def test_mark_visible(reference, oracle):
+    sc, _ = cases.case("s_bg_yaw")
+    d = to_device(sc)
+    ours = _module(d).markVisible(d["means3D"])
+    assert ours.dtype == torch.bool
+    assert torch.equal(ours, reference.mark_visible(d["means3D"], d["viewmatrix"], d["projmatrix"]))
+    assert (np_(ours) == oracle.mark_visible(sc["means3D"], sc["viewmatrix"], sc["projmatrix"])).all()
+
+
+def test_non_default_stream_and_repeat_calls():
+    sc, _ = cases.case("s_deg3")
+    d = to_device(sc)
+    r = _module(d)
+    kw = dict(means3D=d["means3D"], means2D=torch.zeros_like(d["means3D"]), opacities=d["opacities"], shs=d["sh"],
+              scales=d["scales"], rotations=d["rotations"])
+    base, _ = r(**kw)
+    st = torch.cuda.Stream()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(st):
+        other, _ = r(**kw)
+    st.synchronize()
+    assert torch.equal(base, other)
+
+
+def test_sh_degree_growth_uses_stride_M():
+    """active_sh_degree grows during training while the stride stays M (train.py:72-73)."""
+    sc, _ = cases.case("s_deg3")
+    d = to_device(sc)
+    imgs = []
+    for deg in (0, 1, 2, 3):
+        d["sh_degree"] = deg
+        c, _ = _module(d)(means3D=d["means3D"], means2D=torch.zeros_like(d["means3D"]), opacities=d["opacities"],
+                          shs=d["sh"], scales=d["scales"], rotations=d["rotations"])
+        imgs.append(c)
+    assert not torch.equal(imgs[0], imgs[3])
