@@ -160,9 +160,10 @@ __device__ __forceinline__ void sh_to_rgb(int deg, int M, const float* __restric
   (void)M;
   float rr = acc[0] + 0.5f, gg = acc[1] + 0.5f, bb = acc[2] + 0.5f;
   clamped = (rr < 0.f ? 1u : 0u) | (gg < 0.f ? 2u : 0u) | (bb < 0.f ? 4u : 0u);
-  r = fmaxf(rr, 0.f);  // fmaxf(NaN, 0) = 0, like glm::max on the GPU
-  g = fmaxf(gg, 0.f);
-  b = fmaxf(bb, 0.f);
+  // glm::max(x, 0) is (x < 0) ? 0 : x, so a NaN colour stays NaN (forward.cu:70)
+  r = rr < 0.f ? 0.f : rr;
+  g = gg < 0.f ? 0.f : gg;
+  b = bb < 0.f ? 0.f : bb;
 }
 
 template <bool VEC_SH>
@@ -214,6 +215,10 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
     const float sq = __fsqrt_rn(disc);
     const float lmax = fmaxf(__fadd_rn(mid, sq), __fsub_rn(mid, sq));
     const int my_radius = __float2int_rz(ceilf(__fmul_rn(__fsqrt_rn(lmax), 3.0f)));
+    // lambda_max >= 0.3 for finite input, so radius >= 2; radius 0 only arises from a NaN covariance.  The
+    // reference then still counts the Gaussian's tile but never writes its sort key (duplicateWithKeys skips
+    // radii <= 0, rasterizer_impl.cu:84), i.e. it renders an uninitialised key.  Defined behaviour here: culled.
+    if (my_radius <= 0) break;
     const float mx = ndc2pix(projx, cam.W), my = ndc2pix(projy, cam.H);
     int minx, miny, maxx, maxy;
     get_rect(mx, my, my_radius, cam.gx, cam.gy, minx, miny, maxx, maxy);

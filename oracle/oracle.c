@@ -244,8 +244,7 @@ static void sh_to_rgb(int deg, int M, const float* pos, const float* cam,
     #undef SH
     r += 0.5f;
     clamped[c] = (r < 0.0f);
-    rgb[c] = r < 0.0f ? 0.0f : r; /* glm::max(result, 0): NaN -> stays NaN?  max(NaN,0)=0 on GPU */
-    if (isnan(r)) rgb[c] = 0.0f;
+    rgb[c] = r < 0.0f ? 0.0f : r; /* glm::max(x, 0) = (x < 0) ? 0 : x: a NaN colour stays NaN */
   }
 }
 
@@ -376,6 +375,10 @@ long orc_forward(OracleState* s, int P, int D, int M, const float* bg, int W, in
     float l1 = mid + sq, l2 = mid - sq;
     float lmax = fmaxf(l1, l2);
     int my_radius = f2i_ceil(sqrtf(lmax) * 3.0f);
+    /* radius 0 only arises from a NaN covariance (lambda_max >= 0.3 otherwise).  The reference then counts the
+     * tile but never writes its sort key (rasterizer_impl.cu:84 skips radii <= 0) and so sorts an
+     * uninitialised key: undefined.  Oracle and product define it as culled (deviations). */
+    if (my_radius <= 0) continue;
     float px = ndc2pix(projx, W), py = ndc2pix(projy, H);
     int minx, miny, maxx, maxy;
     get_rect(px, py, my_radius, gx, gy, &minx, &miny, &maxx, &maxy);
