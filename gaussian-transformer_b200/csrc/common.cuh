@@ -46,8 +46,7 @@ __host__ __device__ inline size_t align_up(size_t v) { return (v + ALIGN - 1) & 
 //   keys u64[R] (depth bits << 32 | gaussian id, bucketed by tile, unsorted),
 //   point_list u32[R] (sorted gaussian ids)
 // bwd
-//   accA float4[P] dL_dcolor.rgb, dL_dopacity ; accB float4[P] dL_dmean2D.xy,
-//   dL_dconic.xx, .xy ; accC float[P] dL_dconic.yy
+//   acc float[P][12]: dL_dcolor.rgb, dL_dopacity, dL_dmean2D.xy, dL_dconic.xx, .xy, .yy, 3 unused
 struct GeomView {
   float4* g0;
   float4* g1;
@@ -67,9 +66,7 @@ struct BinView {
   uint32_t* point_list;
 };
 struct BwdView {
-  float4* accA;
-  float4* accB;
-  float* accC;
+  float* acc;
 };
 
 // ctrl[] slots
@@ -107,13 +104,11 @@ inline BinView bin_view(void* base, size_t R) {
   v.point_list = (uint32_t*)p;
   return v;
 }
-inline size_t bwd_bytes(size_t P) { return 2 * align_up(16 * P) + align_up(4 * P) + ALIGN; }
+inline size_t bwd_bytes(size_t P) { return align_up(48 * P) + ALIGN; }
 inline BwdView bwd_view(void* base, size_t P) {
-  char* p = (char*)base;
+  (void)P;
   BwdView v;
-  v.accA = (float4*)p; p += align_up(16 * P);
-  v.accB = (float4*)p; p += align_up(16 * P);
-  v.accC = (float*)p;
+  v.acc = (float*)base;
   return v;
 }
 

@@ -223,7 +223,7 @@ int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void
     tile_sort_big_kernel<<<148, 1024, big_smem, stream>>>(im.big_tiles, im.ctrl, im.ranges, b.keys, b.point_list);
     GSR_STAGE("tile_sort_big", in->debug, stream);
   }
-  dim3 grid(cam.gx, cam.gy), block(TILE, TILE);
+  dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
   render_fwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, g.g0, g.g1, g.g2,
                                                 in->colors_precomp, in->bg, im.final_T, im.n_contrib, out_color);
   GSR_STAGE("render_fwd", in->debug, stream);
@@ -253,10 +253,9 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
   BwdView bw = bwd_view(bwd_scratch, (size_t)in->P);
   GSR_CUDA(cudaMemsetAsync(bwd_scratch, 0, bwd_bytes((size_t)in->P), stream), "memset bwd accumulators");
   if (R > 0) {
-    dim3 grid(cam.gx, cam.gy), block(TILE, TILE);
+    dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
     render_bwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0, g.g1, g.g2,
-                                                  in->colors_precomp, im.final_T, im.n_contrib, dL_dpix, bw.accA,
-                                                  bw.accB, bw.accC);
+                                                  in->colors_precomp, im.final_T, im.n_contrib, dL_dpix, bw.acc);
     GSR_STAGE("render_bwd", in->debug, stream);
   }
   BwdOut out;
@@ -271,7 +270,7 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
   out.dL_dconic = dL_dconic;
   preprocess_bwd_kernel<<<(in->P + 255) / 256, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
                                                                 in->rotations, in->sh, in->cov3D_precomp, cam,
-                                                                radii, g.g2, bw.accA, bw.accB, bw.accC, out);
+                                                                radii, g.g2, bw.acc, out);
   GSR_STAGE("preprocess_bwd", in->debug, stream);
   return GSR_OK;
 }

@@ -91,13 +91,13 @@ __device__ __forceinline__ void sh_backward(int deg, int M, const float* __restr
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel(
     int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
     const float* __restrict__ rotations, const float* __restrict__ shs, const float* __restrict__ cov3D_precomp,
-    Cam cam, const int* __restrict__ radii, const float4* __restrict__ g2, const float4* __restrict__ accA,
-    const float4* __restrict__ accB, const float* __restrict__ accC, BwdOut out) {
+    Cam cam, const int* __restrict__ radii, const float4* __restrict__ g2, const float* __restrict__ acc, BwdOut out) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= P) return;
   const size_t I = (size_t)i;
-  const float4 A = accA[i], B = accB[i];
-  const float Cyy = accC[i];
+  const float4* acc4 = reinterpret_cast<const float4*>(acc) + 3 * I;
+  const float4 A = acc4[0], B = acc4[1];
+  const float Cyy = acc4[2].x;
   // quantities the render backward already summed: written for every Gaussian
   out.dL_dcolors[3 * I] = A.x; out.dL_dcolors[3 * I + 1] = A.y; out.dL_dcolors[3 * I + 2] = A.z;
   out.dL_dopacity[I] = A.w;

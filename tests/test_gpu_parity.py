@@ -63,7 +63,10 @@ def _check_image(ours, ref, exact_ncontrib=True):
         assert (diff > IMG_TOL).mean() <= 2e-4 and diff.max() < 2e-2, (diff.max(), (diff > IMG_TOL).mean())
 
 
-def _check_grads(ours, ref, tol=GRAD_TOL):
+def _check_grads(ours, ref, tol=GRAD_TOL, ref_again=None):
+    """ref_again: a second run of the reference on the same inputs.  Its fp32 atomics are order-nondeterministic, so
+    on ill-conditioned Gaussians it differs from ITSELF by more than 1e-3 at 1M Gaussians (measured: rot 1.9e-3,
+    cov3D 6e-4); the bar for a tensor is then max(1e-3, 3 x the reference's own run-to-run deviation)."""
     for k in GRAD_KEYS:
         a, b = np_(ours[k]), np_(ref[k])
         assert a.shape == b.shape or a.size == b.size, (k, a.shape, b.shape)
@@ -72,7 +75,11 @@ def _check_grads(ours, ref, tol=GRAD_TOL):
         fin = np.isfinite(b.reshape(a.shape))
         assert (np.isfinite(a) == fin).all(), k
         e = rel_err(np.where(fin, a, 0), np.where(fin, b.reshape(a.shape), 0))
-        assert e <= tol, (k, e)
+        tol_k = tol
+        if ref_again is not None:
+            tol_k = max(tol, 3.0 * rel_err(np.where(fin, np_(ref_again[k]).reshape(a.shape), 0),
+                                           np.where(fin, b.reshape(a.shape), 0)))
+        assert e <= tol_k, (k, e, tol_k)
 
 
 @pytest.mark.parametrize("name", cases.ALL)
@@ -132,7 +139,9 @@ def test_full_size_vs_reference(P, W, H, reference):
     _check_forward(ours, ref, has_rgb=True)
     _check_image(ours, ref)
     dpix = torch.from_numpy(S.upstream_grad(W, H, seed=1)).cuda()
-    _check_grads(ours_backward(d, ours, dpix), reference.backward(dpix))
+    g_ref = {k: v.clone() for k, v in reference.backward(dpix).items()}
+    reference.forward(d, internals=False)
+    _check_grads(ours_backward(d, ours, dpix), g_ref, ref_again=reference.backward(dpix))
     # size-independent properties
     r = np_(ours["ranges"]).astype(np.int64)
     ne = r[:, 1] > r[:, 0]
