@@ -1,42 +1,167 @@
-// csrc/binning.cuh -- from per-Gaussian rectangles to per-tile depth-sorted lists.
+// csrc/binning.cuh -- from depth-ordered Gaussians to per-tile depth-sorted lists.
 //
-// Replaces, with identical observable results (ranges, point_list):
+// Replaces, with identical observable results (ranges, point_list, num_rendered):
 //   cub::DeviceScan::InclusiveSum + D2H     DGR/cuda_rasterizer/rasterizer_impl.cu:277-281
 //   duplicateWithKeys                       :70-111
 //   cub::DeviceRadixSort::SortPairs (64-bit tile|depth keys, stable)  :300-308
 //   cudaMemset(ranges) + identifyTileRanges :310-318, :116-138
 //
-// B200 design.  The reference globally sorts R (tile|depth) keys with a 6-pass
-// LSD radix sort (~150 B of HBM traffic per instance).  Here the tile part of
-// the key is resolved by *bucketing*: preprocess counts instances per tile, a
-// one-CTA scan turns counts into tile ranges (so `ranges` needs no extra pass),
-// `scatter_instances` drops (depth|id) keys into their tile's bucket with an
-// atomic cursor, and each bucket is sorted on-chip in shared memory.  The
-// reference's stable sort orders equal (tile, depth) keys by emission order,
-// which is ascending Gaussian id (each Gaussian appears at most once per tile),
-// so sorting the 64-bit composite (depth_bits << 32 | id) reproduces its order
-// exactly and needs no stability.  HBM traffic: 8 B written + 8 B read + 4 B
-// written per instance.
+// B200 design.  The reference materialises R = sum(tiles_touched) 12-byte
+// (key, id) pairs and radix-sorts them in 6 passes (~150 B of HBM traffic per
+// instance; R = 12 M at 1 M Gaussians / 1080p).  Here the Gaussians are already
+// in depth order (depth_sort.cuh), so the tile lists can be produced by an
+// ORDER-PRESERVING binning that never forms a key:
+//   1. the depth-ordered sequence is cut into chunks; a warp walks one chunk
+//      sequentially and counts, per tile, how many of its Gaussians cover it
+//      (`bin_pass<false>`): row `chunk` of a chunks x tiles matrix;
+//   2. `column_scan_kernel` turns every column into exclusive prefixes (the
+//      position, inside the tile's list, of the chunk's first instance) and
+//      yields the per-tile totals; `tile_scan_kernel` turns those into `ranges`
+//      and num_rendered -- `ranges` needs no boundary-detection pass;
+//   3. the same walk again (`bin_pass<true>`) with the per-tile cursors
+//      initialised to ranges[tile].x + prefix writes each Gaussian id straight
+//      to its final slot of point_list.
+// A warp handles its chunk strictly in order (one Gaussian at a time, lanes over
+// the tiles of its rectangle), which is what makes the lists come out sorted
+// by (depth, id) without a per-tile sort.  To bound the per-warp cursor table
+// (shared memory) the tile grid is cut into bands of whole tile rows; a warp
+// task is (chunk, band).  HBM traffic: 4 B per instance + the small matrix.
 #pragma once
 #include "common.cuh"
 
 namespace gsr {
 
-constexpr int SORT_SMALL_CAP = 2048;   // keys per tile handled by the 256-thread kernel (16 KB smem)
-constexpr int SORT_BIG_CAP = 24576;    // keys per tile handled by the 1024-thread kernel (192 KB smem)
+constexpr int BIN_WARPS = 4;           // warps per CTA in bin_pass
+constexpr int BAND_TILES_MAX = 4096;   // cursor-table entries per warp (16 KB)
 
-// One CTA: exclusive scan of tile_count -> ranges, zero cursors, collect tiles
-// that need the big / global sort paths, publish R.
+struct BinPlan {
+  int chunk;       // Gaussians per chunk (multiple of 32)
+  int n_chunks;
+  int rows_per_band, n_bands, band_tiles;
+};
+
+inline BinPlan make_bin_plan(int P, int gx, int gy) {
+  BinPlan p;
+  int chunk = (P + 1023) / 1024;          // at most 1024 chunks ...
+  if (chunk < 1024) chunk = 1024;         // ... of at least 1024 Gaussians
+  chunk = (chunk + 31) & ~31;
+  p.chunk = chunk;
+  p.n_chunks = P > 0 ? (P + chunk - 1) / chunk : 0;
+  p.rows_per_band = BAND_TILES_MAX / gx;
+  if (p.rows_per_band < 1) p.rows_per_band = 0;  // image wider than 65536 px: unsupported, caller reports it
+  if (p.rows_per_band > gy) p.rows_per_band = gy;
+  p.n_bands = p.rows_per_band ? (gy + p.rows_per_band - 1) / p.rows_per_band : 0;
+  p.band_tiles = p.rows_per_band * gx;
+  return p;
+}
+
+// One warp per (chunk, band).  SCATTER = false: count into matrix[chunk][tile];
+// SCATTER = true: cursors start at ranges[tile].x + matrix[chunk][tile] and ids are written to point_list.
+template <bool SCATTER>
+__global__ void __launch_bounds__(BIN_WARPS * 32) bin_pass_kernel(int P, const uint32_t* __restrict__ order,
+                                                                  const float4* __restrict__ g0, int gx, int gy,
+                                                                  BinPlan plan, uint32_t* __restrict__ matrix,
+                                                                  const uint2* __restrict__ ranges,
+                                                                  uint32_t* __restrict__ point_list) {
+  extern __shared__ uint32_t s_tab[];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int task = blockIdx.x * BIN_WARPS + w;
+  if (task >= plan.n_chunks * plan.n_bands) return;
+  const int chunk = task / plan.n_bands, band = task - chunk * plan.n_bands;
+  const int by0 = band * plan.rows_per_band, by1 = min(gy, by0 + plan.rows_per_band);
+  const int ntab = (by1 - by0) * gx;
+  const int tile0 = by0 * gx;
+  uint32_t* tab = s_tab + w * plan.band_tiles;
+  uint32_t* row = matrix + (size_t)chunk * gx * gy + tile0;
+  for (int t = lane; t < ntab; t += 32) tab[t] = SCATTER ? (__ldg(&ranges[tile0 + t].x) + row[t]) : 0u;
+  __syncwarp();
+  const int begin = chunk * plan.chunk, end = min(P, begin + plan.chunk);
+  for (int r0 = begin; r0 < end; r0 += 32) {
+    const int k = r0 + lane;
+    uint32_t id = 0;
+    int minx = 0, maxx = 0, y0 = 0, y1 = 0;
+    if (k < end) {
+      id = __ldg(order + k);
+      const float4 a = __ldg(g0 + id);
+      const int radius = __float_as_int(a.w);
+      if (radius > 0) {
+        int miny, maxy;
+        // same rectangle as duplicateWithKeys recomputes (rasterizer_impl.cu:85-90)
+        get_rect(a.x, a.y, radius, gx, gy, minx, miny, maxx, maxy);
+        y0 = max(miny, by0);
+        y1 = min(maxy, by1);
+      }
+    }
+    unsigned live = __ballot_sync(0xffffffffu, (y1 > y0) && (maxx > minx));
+    while (live) {
+      const int src = __ffs(live) - 1;
+      live &= live - 1;
+      const uint32_t gid = __shfl_sync(0xffffffffu, id, src);
+      const int x0 = __shfl_sync(0xffffffffu, minx, src), x1 = __shfl_sync(0xffffffffu, maxx, src);
+      const int ya = __shfl_sync(0xffffffffu, y0, src), yb = __shfl_sync(0xffffffffu, y1, src);
+      const int wdt = x1 - x0, nt = wdt * (yb - ya);
+      const int rowbase = (ya - by0) * gx + x0;
+      if (nt <= 32) {
+        if (lane < nt) {
+          const int ty = __float2int_rz(((float)lane + 0.5f) * __frcp_rn((float)wdt));  // exact for lane, wdt <= 32
+          const int idx = rowbase + ty * gx + (lane - ty * wdt);
+          const uint32_t v = tab[idx];
+          tab[idx] = v + 1u;
+          if (SCATTER) point_list[v] = gid;
+        }
+      } else {
+        for (int t = lane; t < nt; t += 32) {
+          const int ty = t / wdt;
+          const int idx = rowbase + ty * gx + (t - ty * wdt);
+          const uint32_t v = tab[idx];
+          tab[idx] = v + 1u;
+          if (SCATTER) point_list[v] = gid;
+        }
+      }
+      __syncwarp();
+    }
+  }
+  if (!SCATTER) {
+    __syncwarp();
+    for (int t = lane; t < ntab; t += 32) row[t] = tab[t];
+  }
+}
+
+// matrix[chunk][tile] -> exclusive prefix over chunks (in place); tile_count[tile] = column total.
+// CTA = 32 tiles x 8 chunk groups.
+__global__ void __launch_bounds__(256) column_scan_kernel(uint32_t* __restrict__ matrix, int n_chunks, int T,
+                                                          uint32_t* __restrict__ tile_count) {
+  __shared__ uint32_t part[8][33];
+  const int tx = threadIdx.x & 31, g = threadIdx.x >> 5;
+  const int tile = blockIdx.x * 32 + tx;
+  const int per = (n_chunks + 7) / 8;
+  const int c0 = min(n_chunks, g * per), c1 = min(n_chunks, c0 + per);
+  uint32_t sum = 0;
+  if (tile < T)
+    for (int c = c0; c < c1; c++) sum += matrix[(size_t)c * T + tile];
+  part[g][tx] = sum;
+  __syncthreads();
+  uint32_t run = 0;
+  for (int gg = 0; gg < g; gg++) run += part[gg][tx];
+  if (tile < T) {
+    for (int c = c0; c < c1; c++) {
+      const size_t i = (size_t)c * T + tile;
+      const uint32_t v = matrix[i];
+      matrix[i] = run;
+      run += v;
+    }
+    if (g == 7) tile_count[tile] = run;
+  }
+}
+
+// One CTA: exclusive scan of tile_count -> ranges ((0,0) for empty tiles, like the reference's memset +
+// identifyTileRanges), publish R = num_rendered.
 __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* __restrict__ tile_count,
-                                                         uint2* __restrict__ ranges,
-                                                         uint32_t* __restrict__ tile_cursor,
-                                                         uint32_t* __restrict__ big_tiles,
-                                                         uint32_t* __restrict__ ctrl) {
+                                                         uint2* __restrict__ ranges, uint32_t* __restrict__ ctrl) {
   __shared__ unsigned long long warp_tot[32];
   __shared__ unsigned long long carry_s;
-  __shared__ uint32_t nbig_s;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  if (tid == 0) { carry_s = 0ull; nbig_s = 0u; }
+  if (tid == 0) carry_s = 0ull;
   __syncthreads();
   for (int base = 0; base < T; base += 1024) {
     const int t = base + tid;
@@ -44,173 +169,36 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
     unsigned long long v = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      unsigned long long n = __shfl_up_sync(0xffffffffu, v, o);
-      if (lane >= o) v += n;
+      const unsigned long long nb = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += nb;
     }
     if (lane == 31) warp_tot[wid] = v;
     __syncthreads();
     if (wid == 0) {
-      unsigned long long w = warp_tot[lane];
+      unsigned long long ws = warp_tot[lane];
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
-        unsigned long long n = __shfl_up_sync(0xffffffffu, w, o);
-        if (lane >= o) w += n;
+        const unsigned long long nb = __shfl_up_sync(0xffffffffu, ws, o);
+        if (lane >= o) ws += nb;
       }
-      warp_tot[lane] = w;  // inclusive over warps
+      warp_tot[lane] = ws;
     }
     __syncthreads();
-    const unsigned long long carry = carry_s;
-    const unsigned long long incl = carry + v + (wid > 0 ? warp_tot[wid - 1] : 0ull);
+    const unsigned long long incl = carry_s + v + (wid > 0 ? warp_tot[wid - 1] : 0ull);
     if (t < T) {
       const unsigned long long excl = incl - c;
       // saturate: an overflowing R is reported through ctrl and never rendered
       const uint32_t lo = excl > 0xffffffffull ? 0xffffffffu : (uint32_t)excl;
       const uint32_t hi = incl > 0xffffffffull ? 0xffffffffu : (uint32_t)incl;
       ranges[t] = c ? make_uint2(lo, hi) : make_uint2(0u, 0u);
-      tile_cursor[t] = 0u;
-      if (c > (uint32_t)SORT_SMALL_CAP) big_tiles[atomicAdd(&nbig_s, 1u)] = (uint32_t)t;
     }
     __syncthreads();
     if (tid == 1023) carry_s = incl;
     __syncthreads();
   }
   if (tid == 0) {
-    const unsigned long long R = carry_s;
-    ctrl[CTRL_R_LO] = (uint32_t)(R & 0xffffffffull);
-    ctrl[CTRL_R_HI] = (uint32_t)(R >> 32);
-    ctrl[CTRL_NBIG] = nbig_s;
-  }
-}
-
-// Per visible Gaussian: recompute its rectangle from (mean2D, radius) exactly as
-// duplicateWithKeys does (rasterizer_impl.cu:85-90) and append (depth|id) to
-// each covered tile's bucket.
-__global__ void __launch_bounds__(256) scatter_instances_kernel(int P, const float4* __restrict__ g0, int gx, int gy,
-                                                                const uint2* __restrict__ ranges,
-                                                                uint32_t* __restrict__ tile_cursor,
-                                                                unsigned long long* __restrict__ keys) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= P) return;
-  const float4 a = __ldg(g0 + i);
-  const int radius = __float_as_int(a.w);
-  if (radius <= 0) return;
-  int minx, miny, maxx, maxy;
-  get_rect(a.x, a.y, radius, gx, gy, minx, miny, maxx, maxy);
-  const unsigned long long key = ((unsigned long long)__float_as_uint(a.z) << 32) | (uint32_t)i;
-  for (int y = miny; y < maxy; y++)
-    for (int x = minx; x < maxx; x++) {
-      const int t = y * gx + x;
-      const uint32_t slot = __ldg(&ranges[t].x) + atomicAdd(&tile_cursor[t], 1u);
-      keys[slot] = key;
-    }
-}
-
-// Bitonic network with all comparators ascending (mirror step + half cleaners):
-// positions >= n behave as +inf and never move, so any n works without padding.
-template <int THREADS>
-__device__ __forceinline__ void bitonic_sort_shared(unsigned long long* s, int n) {
-  int N = 1;
-  while (N < n) N <<= 1;
-  const int half = N >> 1;
-  for (int k = 2; k <= N; k <<= 1) {
-    // mirror step: i in lower half of each k-block, partner = i ^ (k-1)
-    {
-      const int hk = k >> 1;
-      for (int c = threadIdx.x; c < half; c += THREADS) {
-        const int i = (c / hk) * k + (c % hk);
-        const int p = i ^ (k - 1);
-        if (p < n) {
-          unsigned long long a = s[i], b = s[p];
-          if (a > b) { s[i] = b; s[p] = a; }
-        }
-      }
-      __syncthreads();
-    }
-    for (int j = k >> 2; j > 0; j >>= 1) {
-      for (int c = threadIdx.x; c < half; c += THREADS) {
-        const int i = (c / j) * (2 * j) + (c % j);
-        const int p = i + j;
-        if (p < n) {
-          unsigned long long a = s[i], b = s[p];
-          if (a > b) { s[i] = b; s[p] = a; }
-        }
-      }
-      __syncthreads();
-    }
-  }
-}
-
-template <int THREADS>
-__device__ __forceinline__ void sort_one_tile_shared(unsigned long long* s, const unsigned long long* __restrict__ keys,
-                                                     uint32_t* __restrict__ point_list, uint32_t start, int n) {
-  for (int i = threadIdx.x; i < n; i += THREADS) s[i] = keys[start + i];
-  __syncthreads();
-  bitonic_sort_shared<THREADS>(s, n);
-  for (int i = threadIdx.x; i < n; i += THREADS) point_list[start + i] = (uint32_t)s[i];
-  __syncthreads();
-}
-
-// One CTA per tile, lists up to SORT_SMALL_CAP.
-__global__ void __launch_bounds__(256) tile_sort_small_kernel(const uint2* __restrict__ ranges,
-                                                              const unsigned long long* __restrict__ keys,
-                                                              uint32_t* __restrict__ point_list) {
-  __shared__ unsigned long long s[SORT_SMALL_CAP];
-  const uint2 r = ranges[blockIdx.x];
-  const int n = (int)(r.y - r.x);
-  if (n <= 0 || n > SORT_SMALL_CAP) return;
-  if (n == 1) {
-    if (threadIdx.x == 0) point_list[r.x] = (uint32_t)keys[r.x];
-    return;
-  }
-  sort_one_tile_shared<256>(s, keys, point_list, r.x, n);
-}
-
-// Persistent grid over the (rare) tiles with long lists: <= SORT_BIG_CAP keys are
-// sorted in 192 KB of shared memory; longer lists fall back to the same network
-// run in place in global memory (correct for any n, slow, practically unused).
-__global__ void __launch_bounds__(1024) tile_sort_big_kernel(const uint32_t* __restrict__ big_tiles,
-                                                             const uint32_t* __restrict__ ctrl,
-                                                             const uint2* __restrict__ ranges,
-                                                             unsigned long long* __restrict__ keys,
-                                                             uint32_t* __restrict__ point_list) {
-  extern __shared__ __align__(16) unsigned long long sbig[];
-  const uint32_t nbig = ctrl[CTRL_NBIG];
-  for (uint32_t b = blockIdx.x; b < nbig; b += gridDim.x) {
-    const uint2 r = ranges[big_tiles[b]];
-    const int n = (int)(r.y - r.x);
-    if (n <= SORT_BIG_CAP) {
-      sort_one_tile_shared<1024>(sbig, keys, point_list, r.x, n);
-    } else {
-      unsigned long long* g = keys + r.x;
-      long long N = 1;
-      while (N < n) N <<= 1;
-      const long long half = N >> 1;
-      for (long long k = 2; k <= N; k <<= 1) {
-        const long long hk = k >> 1;
-        for (long long c = threadIdx.x; c < half; c += 1024) {
-          const long long i = (c / hk) * k + (c % hk);
-          const long long p = i ^ (k - 1);
-          if (p < n) {
-            unsigned long long a = g[i], q = g[p];
-            if (a > q) { g[i] = q; g[p] = a; }
-          }
-        }
-        __syncthreads();
-        for (long long j = k >> 2; j > 0; j >>= 1) {
-          for (long long c = threadIdx.x; c < half; c += 1024) {
-            const long long i = (c / j) * (2 * j) + (c % j);
-            const long long p = i + j;
-            if (p < n) {
-              unsigned long long a = g[i], q = g[p];
-              if (a > q) { g[i] = q; g[p] = a; }
-            }
-          }
-          __syncthreads();
-        }
-      }
-      for (int i = threadIdx.x; i < n; i += 1024) point_list[r.x + i] = (uint32_t)g[i];
-      __syncthreads();
-    }
+    ctrl[CTRL_R_LO] = (uint32_t)(carry_s & 0xffffffffull);
+    ctrl[CTRL_R_HI] = (uint32_t)(carry_s >> 32);
   }
 }
 

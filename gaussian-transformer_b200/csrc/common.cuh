@@ -34,35 +34,36 @@ constexpr size_t ALIGN = 256;
 __host__ __device__ inline size_t align_up(size_t v) { return (v + ALIGN - 1) & ~(ALIGN - 1); }
 
 // ---------------------------------------------------------------- scratch layout
-// geom  (per Gaussian, written by preprocess_fwd, read by scatter / render / bwd)
+// geom  (per Gaussian, written by preprocess_fwd, read by binning / render / bwd)
 //   g0 float4[P]  mean2D.x, mean2D.y, depth, radius (int bits)
 //   g1 float4[P]  conic.x, conic.y, conic.z, opacity
 //   g2 float4[P]  r, g, b, flags (bits 0..2 = clamped r/g/b, bits 3.. = tiles_touched)
+//   keys[2] u32[P], vals[2] u32[P]  depth-sort ping-pong (keys = depth bits, 0xffffffff for culled)
+//   cta_hist u32[256 * n_sort_cta]  radix digit histograms
 // image
-//   final_T f32[N], n_contrib u32[N], ranges uint2[T], tile_count u32[T],
-//   tile_cursor u32[T], big_tiles u32[T] (ids of tiles whose list does not fit
-//   the small sort kernel), ctrl u32[64] (counters / flags)
+//   final_T f32[N], n_contrib u32[N], ranges uint2[T], tile_count u32[T], ctrl u32[64],
+//   matrix u32[n_chunks * T] (binning.cuh)
 // binning
-//   keys u64[R] (depth bits << 32 | gaussian id, bucketed by tile, unsorted),
-//   point_list u32[R] (sorted gaussian ids)
+//   point_list u32[R] (depth-sorted gaussian ids, tile after tile)
 // bwd
 //   acc float[P][12]: dL_dcolor.rgb, dL_dopacity, dL_dmean2D.xy, dL_dconic.xx, .xy, .yy, 3 unused
 struct GeomView {
   float4* g0;
   float4* g1;
   float4* g2;
+  uint32_t* keys[2];
+  uint32_t* vals[2];
+  uint32_t* cta_hist;
 };
 struct ImageView {
   float* final_T;
   uint32_t* n_contrib;
   uint2* ranges;
   uint32_t* tile_count;
-  uint32_t* tile_cursor;
-  uint32_t* big_tiles;
   uint32_t* ctrl;
+  uint32_t* matrix;
 };
 struct BinView {
-  unsigned long long* keys;
   uint32_t* point_list;
 };
 struct BwdView {
@@ -70,19 +71,36 @@ struct BwdView {
 };
 
 // ctrl[] slots
-enum { CTRL_FLAGS = 0, CTRL_NBIG = 1, CTRL_NHUGE = 2, CTRL_R_LO = 4, CTRL_R_HI = 5, CTRL_WORDS = 64 };
+enum { CTRL_FLAGS = 0, CTRL_R_LO = 4, CTRL_R_HI = 5, CTRL_WORDS = 64 };
 
-inline size_t geom_bytes(size_t P) { return 3 * align_up(16 * P) + ALIGN; }
+constexpr int SORT_TILE_KEYS = 4096;  // keys per CTA in depth_sort.cuh (RS_TILE)
+inline size_t sort_ctas(size_t P) { return (P + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS; }
+inline size_t bin_chunks(size_t P) {  // must match make_bin_plan (binning.cuh)
+  size_t chunk = (P + 1023) / 1024;
+  if (chunk < 1024) chunk = 1024;
+  chunk = (chunk + 31) & ~(size_t)31;
+  return P ? (P + chunk - 1) / chunk : 0;
+}
+
+inline size_t geom_bytes(size_t P) {
+  return 3 * align_up(16 * P) + 4 * align_up(4 * P) + align_up(4 * 256 * sort_ctas(P)) + ALIGN;
+}
 inline GeomView geom_view(void* base, size_t P) {
   char* p = (char*)base;
   GeomView v;
   v.g0 = (float4*)p; p += align_up(16 * P);
   v.g1 = (float4*)p; p += align_up(16 * P);
-  v.g2 = (float4*)p;
+  v.g2 = (float4*)p; p += align_up(16 * P);
+  v.keys[0] = (uint32_t*)p; p += align_up(4 * P);
+  v.keys[1] = (uint32_t*)p; p += align_up(4 * P);
+  v.vals[0] = (uint32_t*)p; p += align_up(4 * P);
+  v.vals[1] = (uint32_t*)p; p += align_up(4 * P);
+  v.cta_hist = (uint32_t*)p;
   return v;
 }
-inline size_t image_bytes(size_t N, size_t T) {
-  return 2 * align_up(4 * N) + align_up(8 * T) + 3 * align_up(4 * T) + align_up(4 * CTRL_WORDS) + ALIGN;
+inline size_t image_bytes(size_t N, size_t T, size_t P) {
+  return 2 * align_up(4 * N) + align_up(8 * T) + align_up(4 * T) + align_up(4 * CTRL_WORDS) +
+         align_up(4 * T * bin_chunks(P)) + ALIGN;
 }
 inline ImageView image_view(void* base, size_t N, size_t T) {
   char* p = (char*)base;
@@ -91,17 +109,15 @@ inline ImageView image_view(void* base, size_t N, size_t T) {
   v.n_contrib = (uint32_t*)p; p += align_up(4 * N);
   v.ranges = (uint2*)p; p += align_up(8 * T);
   v.tile_count = (uint32_t*)p; p += align_up(4 * T);
-  v.tile_cursor = (uint32_t*)p; p += align_up(4 * T);
-  v.big_tiles = (uint32_t*)p; p += align_up(4 * T);
-  v.ctrl = (uint32_t*)p;
+  v.ctrl = (uint32_t*)p; p += align_up(4 * CTRL_WORDS);
+  v.matrix = (uint32_t*)p;
   return v;
 }
-inline size_t bin_bytes(size_t R) { return align_up(8 * R) + align_up(4 * R) + ALIGN; }
+inline size_t bin_bytes(size_t R) { return align_up(4 * R) + ALIGN; }
 inline BinView bin_view(void* base, size_t R) {
-  char* p = (char*)base;
+  (void)R;
   BinView v;
-  v.keys = (unsigned long long*)p; p += align_up(8 * R);
-  v.point_list = (uint32_t*)p;
+  v.point_list = (uint32_t*)base;
   return v;
 }
 inline size_t bwd_bytes(size_t P) { return align_up(48 * P) + ALIGN; }

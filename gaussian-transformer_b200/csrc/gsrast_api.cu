@@ -10,6 +10,7 @@
 #include "../../include/gsrast.h"
 #include "binning.cuh"
 #include "common.cuh"
+#include "depth_sort.cuh"
 #include "preprocess_bwd.cuh"
 #include "preprocess_fwd.cuh"
 #include "render_bwd.cuh"
@@ -107,7 +108,7 @@ int gsr_scratch_bytes(int32_t P, int64_t R, int32_t W, int32_t H, size_t* geom, 
   const size_t T = (size_t)((W + TILE - 1) / TILE) * ((H + TILE - 1) / TILE);
   if (geom) *geom = geom_bytes((size_t)P);
   if (binning) *binning = bin_bytes((size_t)R);
-  if (image) *image = image_bytes(N, T);
+  if (image) *image = image_bytes(N, T, (size_t)P);
   if (bwd) *bwd = bwd_bytes((size_t)P);
   return GSR_OK;
 }
@@ -165,8 +166,8 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   const size_t N = (size_t)in->W * in->H, T = (size_t)cam.gx * cam.gy;
   GeomView g = geom_view(geom, (size_t)in->P);
   ImageView im = image_view(image, N, T);
-  // tile_count[T] and ctrl are zeroed; tile_cursor / big_tiles are written by the scan
-  GSR_CUDA(cudaMemsetAsync(im.tile_count, 0, 4 * T, stream), "memset tile_count");
+  const BinPlan plan = make_bin_plan(in->P, cam.gx, cam.gy);
+  if (plan.n_bands == 0) return fail(GSR_ERR_INVALID, "image wider than 65536 pixels is not supported");
   GSR_CUDA(cudaMemsetAsync(im.ctrl, 0, 4 * CTRL_WORDS, stream), "memset ctrl");
   const int K = (in->D + 1) * (in->D + 1);
   const bool vec_sh = in->sh && !in->colors_precomp && ((K * 3) % 4 == 0) && ((in->M * 12) % 16 == 0) &&
@@ -176,14 +177,34 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
     preprocess_fwd_kernel<true><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
                                                             in->rotations, in->opacities, in->sh,
                                                             in->colors_precomp, in->cov3D_precomp, cam,
-                                                            in->prefiltered, radii, g, im.tile_count, im.ctrl);
+                                                            in->prefiltered, radii, g, im.ctrl);
   else
     preprocess_fwd_kernel<false><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
                                                              in->rotations, in->opacities, in->sh,
                                                              in->colors_precomp, in->cov3D_precomp, cam,
-                                                             in->prefiltered, radii, g, im.tile_count, im.ctrl);
+                                                             in->prefiltered, radii, g, im.ctrl);
   GSR_STAGE("preprocess_fwd", in->debug, stream);
-  tile_scan_kernel<<<1, 1024, 0, stream>>>((int)T, im.tile_count, im.ranges, im.tile_cursor, im.big_tiles, im.ctrl);
+  // depth sort of the P Gaussians: 4 stable 8-bit passes, result in keys[0] / vals[0]
+  const int n_cta = (int)sort_ctas((size_t)in->P);
+  for (int pass = 0; pass < 4; pass++) {
+    const int src = pass & 1, dst = src ^ 1, shift = 8 * pass;
+    radix_hist_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], in->P, shift, n_cta, g.cta_hist);
+    exclusive_scan_kernel<<<1, 1024, 0, stream>>>(g.cta_hist, 256 * n_cta, nullptr);
+    radix_scatter_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], pass == 0 ? nullptr : g.vals[src], in->P,
+                                                          shift, n_cta, g.cta_hist, g.keys[dst], g.vals[dst]);
+    GSR_STAGE("depth_sort", in->debug, stream);
+  }
+  // order-preserving binning, counting half
+  const int tasks = plan.n_chunks * plan.n_bands;
+  const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
+  GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
+           "bin_pass smem attribute");
+  bin_pass_kernel<false><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
+      in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, nullptr);
+  GSR_STAGE("bin_count", in->debug, stream);
+  column_scan_kernel<<<((int)T + 31) / 32, 256, 0, stream>>>(im.matrix, plan.n_chunks, (int)T, im.tile_count);
+  GSR_STAGE("column_scan", in->debug, stream);
+  tile_scan_kernel<<<1, 1024, 0, stream>>>((int)T, im.tile_count, im.ranges, im.ctrl);
   GSR_STAGE("tile_scan", in->debug, stream);
   // ctrl[CTRL_R_LO..HI] -> host_result[0] (little endian int64), flags -> [1]
   GSR_CUDA(cudaMemcpyAsync(&host_result[0], im.ctrl + CTRL_R_LO, 8, cudaMemcpyDeviceToHost, stream), "copy R");
@@ -211,17 +232,14 @@ int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void
   ImageView im = image_view(image, N, T);
   BinView b = bin_view(binning, (size_t)R);
   if (R > 0) {
-    scatter_instances_kernel<<<(in->P + 255) / 256, 256, 0, stream>>>(in->P, g.g0, cam.gx, cam.gy, im.ranges,
-                                                                     im.tile_cursor, b.keys);
-    GSR_STAGE("scatter_instances", in->debug, stream);
-    tile_sort_small_kernel<<<(unsigned)T, 256, 0, stream>>>(im.ranges, b.keys, b.point_list);
-    GSR_STAGE("tile_sort_small", in->debug, stream);
-    const int big_smem = SORT_BIG_CAP * 8;
-    // per-device function attribute; a few hundred ns, so simply applied on every call (no global state)
-    GSR_CUDA(cudaFuncSetAttribute(tile_sort_big_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, big_smem),
-             "tile_sort_big smem attribute");
-    tile_sort_big_kernel<<<148, 1024, big_smem, stream>>>(im.big_tiles, im.ctrl, im.ranges, b.keys, b.point_list);
-    GSR_STAGE("tile_sort_big", in->debug, stream);
+    const BinPlan plan = make_bin_plan(in->P, cam.gx, cam.gy);
+    const int tasks = plan.n_chunks * plan.n_bands;
+    const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
+    GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
+             "bin_pass smem attribute");
+    bin_pass_kernel<true><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
+        in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list);
+    GSR_STAGE("bin_scatter", in->debug, stream);
   }
   dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
   render_fwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, g.g0, g.g1, g.g2,

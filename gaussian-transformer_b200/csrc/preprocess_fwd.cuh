@@ -6,10 +6,9 @@
 // round-to-nearest intrinsic placed where the reference's compiled code rounds.
 //
 // B200 design: one thread per Gaussian, float4 stores of three SoA records, SH
-// coefficients fetched with 128-bit read-only loads, per-tile instance counts
-// accumulated with fire-and-forget REDs (this replaces the reference's
-// per-Gaussian prefix sum + 64-bit key sort: instances are bucketed by tile and
-// each bucket is depth-sorted in shared memory, see binning.cuh).
+// coefficients fetched with 128-bit read-only loads; also emits the 32-bit
+// depth key the Gaussian-level sort consumes (depth_sort.cuh) -- the reference's
+// per-Gaussian prefix sum + 64-bit per-instance key sort has no counterpart.
 #pragma once
 #include "common.cuh"
 
@@ -171,7 +170,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
     int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
     const float* __restrict__ rotations, const float* __restrict__ opacities, const float* __restrict__ shs,
     const float* __restrict__ colors_precomp, const float* __restrict__ cov3D_precomp, Cam cam, int prefiltered,
-    int* __restrict__ radii, GeomView geom, uint32_t* __restrict__ tile_count, uint32_t* __restrict__ ctrl) {
+    int* __restrict__ radii, GeomView geom, uint32_t* __restrict__ ctrl) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= P) return;
   int out_radius = 0;
@@ -234,15 +233,13 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
       const float dx = px3 - __ldg(cam.campos), dy = py3 - __ldg(cam.campos + 1), dz = pz3 - __ldg(cam.campos + 2);
       sh_to_rgb<VEC_SH>(D, M, shs + (size_t)i * M * 3, dx, dy, dz, r, g, bl, clamped);
     }
-    // per-tile instance counts (fire-and-forget REDs)
-    for (int y = miny; y < maxy; y++)
-      for (int x = minx; x < maxx; x++) atomicAdd(&tile_count[y * cam.gx + x], 1u);
     out_radius = my_radius;
     o0 = make_float4(mx, my, vz, __int_as_float(my_radius));
     o1 = make_float4(conx, cony, conz, __ldg(opacities + i));
     o2 = make_float4(r, g, bl, __uint_as_float(((uint32_t)tiles << 3) | clamped));
   } while (0);
   radii[i] = out_radius;
+  geom.keys[0][i] = out_radius > 0 ? __float_as_uint(o0.z) : 0xffffffffu;  // depth-sort key (depth_sort.cuh)
   geom.g0[i] = o0;
   geom.g1[i] = o1;
   geom.g2[i] = o2;

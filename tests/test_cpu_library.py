@@ -23,7 +23,7 @@ def test_library_exports_every_declared_symbol():
 def test_scratch_bytes_and_error_reporting():
     from diff_gaussian_rasterization import _lib
     g, b, i, w = _lib.scratch_bytes(1_000_000, 5_000_000, 1920, 1080)
-    assert g >= 48 * 1_000_000 and b >= 12 * 5_000_000 and i >= 8 * 1920 * 1080 and w >= 36 * 1_000_000
+    assert g >= 48 * 1_000_000 and b >= 4 * 5_000_000 and i >= 8 * 1920 * 1080 and w >= 36 * 1_000_000
     assert all(x % 256 == 0 for x in (g, b, i, w))
     with pytest.raises(RuntimeError, match="bad sizes"):
         _lib.scratch_bytes(-1, 0, 16, 16)
