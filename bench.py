@@ -1,0 +1,331 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the hot path (rasterize_gaussians forward+backward).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  (N > 1: launched by `python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...`)
+
+Workload (BASELINE.json configs[1], "C2"): synthetic scene S, 1,000,000 Gaussians, SH degree 3,
+1920x1080, one view; a step = one forward+backward of rasterize_gaussians through the public API
+(GaussianRasterizer + autograd).  With N > 1 every rank renders its own view of the replicated Gaussians (cameras on
+a 30-degree arc) and the per-Gaussian gradients are summed with an NCCL all-reduce: weak scaling, value = views/s over
+all ranks.  Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path[:0] = [os.path.join(ROOT, "gaussian-transformer_b200"), os.path.join(ROOT, "tests")]
+
+P_GAUSS, WIDTH, HEIGHT, SH_DEG, M_COEF = 1_000_000, 1920, 1080, 3, 16
+METRIC = "fwd+bwd iters/s (rasterize_gaussians, 1M Gaussians SH3, 1920x1080)"
+UNIT = "iters/s"
+TENSORS = ("means3D", "scales", "rotations", "opacities", "sh", "bg", "viewmatrix", "projmatrix", "campos")
+LEAVES = ("means3D", "sh", "opacities", "scales", "rotations")
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~10-20 s CPU oracle timing")
+    return ap.parse_args()
+
+
+def peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"], "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "50"], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for line in self.f.read().splitlines():
+            c = [x.strip() for x in line.split(",")]
+            if len(c) < 7:
+                continue
+            try:
+                sm.append(float(c[0]))
+                mx.append(float(c[1]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        if sm:
+            out.update(sm_mhz=float(np.median(sm)), sm_max_mhz=float(max(mx)), reasons=sorted(reasons),
+                       samples=len(sm))
+        return out
+
+
+def algorithmic_bytes(P, V, R, N, K, M):
+    """SURVEY.md 8(d) / DESIGN.md: compulsory HBM bytes of one fwd+bwd iteration, per stage and in total."""
+    a_fwd = 16 * P + (68 + 12 * K) * V + 60 * R + 20 * N
+    a_bwd = 20 * N + 40 * R + (116 + 12 * K) * V + (56 + 12 * M) * P
+    per_stage = {
+        "preprocess_fwd": 16 * P + (32 + 12 * K) * V + 36 * V,
+        "render_fwd": 4 * R + 36 * R + 20 * N,
+        "render_bwd": 20 * N + 4 * R + 36 * R + 36 * V,
+        "preprocess_bwd": 36 * V + (44 + 12 * K) * V + (56 + 12 * M) * P,
+    }
+    return a_fwd + a_bwd, per_stage
+
+
+def make_scene(rank, world):
+    import gsr_scenes as S
+    yaw = 0.0 if world == 1 else -15.0 + 30.0 * rank / (world - 1)
+    sc = S.scene_S(P_GAUSS, WIDTH, HEIGHT, seed=0, M=M_COEF, sh_degree=SH_DEG, yaw_deg=yaw)
+    return sc, S.upstream_grad(WIDTH, HEIGHT, seed=1)
+
+
+def cpu_baseline(sc, dpix):
+    """The oracle port (oracle/oracle.c, OpenMP over all host cores) timed on ONE full iteration of the same workload
+    (~10-20 s of CPU work)."""
+    from checkers import Oracle
+    orc = Oracle()
+    t0 = time.time()
+    orc.forward(sc, internals=False)
+    orc.backward(dpix)
+    dt = time.time() - t0
+    return {"value": 1.0 / dt, "unit": UNIT, "cores": orc.num_threads(), "kind": "port",
+            "sample": "1 full fwd+bwd iteration of the same workload (oracle/oracle.c, OpenMP), %.1f s" % dt}
+
+
+def run_reference(args, rank, world):
+    """Reference arm: the UNMODIFIED reference rasterizer (oracle/_ref, its own CUDA kernels) on the same box and
+    workload; if that library is absent, the CPU oracle port."""
+    if rank != 0:
+        return None
+    sc, dpix = make_scene(0, 1)
+    line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "config": {"workload": "C2: scene S, 1M Gaussians, SH degree 3, 1920x1080, 1 view, "
+                                                        "fwd+bwd", "P": P_GAUSS, "W": WIDTH, "H": HEIGHT}}
+    from checkers import REF_SO
+    import torch
+    if os.path.exists(REF_SO) and torch.cuda.is_available():
+        from checkers import Reference
+        from util import to_device
+        torch.cuda.set_device(0)
+        d = to_device(sc)
+        g = torch.from_numpy(dpix).cuda()
+        ref = Reference()
+
+        def step():
+            ref.forward(d, internals=False, sync=False)
+            ref.backward(g, sync=False)
+        for _ in range(max(args.warmup, 3)):
+            step()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(args.steps):
+            step()
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / args.steps
+        v = 1000.0 / ms
+        line.update(value=v, ms_per_step=ms, gaussians_per_s=v * P_GAUSS,
+                    cpu_baseline={"value": v, "unit": UNIT, "cores": 0, "kind": "reference",
+                                  "sample": "the unmodified reference CUDA rasterizer (oracle/_ref, built from "
+                                            "/root/reference sources) on the same B200, full workload, inputs "
+                                            "resident; it has no CPU implementation"})
+    else:
+        cb = cpu_baseline(sc, dpix)
+        line.update(value=cb["value"], ms_per_step=1000.0 / cb["value"], gaussians_per_s=cb["value"] * P_GAUSS,
+                    cpu_baseline=cb)
+    line["e2e"] = {"value": line["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    return line
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer, _lib
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    sc, dpix_np = make_scene(rank, world)
+    host = {k: torch.from_numpy(np.ascontiguousarray(sc[k])).pin_memory() for k in TENSORS}
+    t = {k: v.to(dev) for k, v in host.items()}
+    dpix_host = torch.from_numpy(dpix_np).pin_memory()
+    dpix = dpix_host.to(dev)
+    settings = GaussianRasterizationSettings(HEIGHT, WIDTH, sc["tanfovx"], sc["tanfovy"], t["bg"], 1.0,
+                                             t["viewmatrix"], t["projmatrix"], SH_DEG, t["campos"], False, False)
+    raster = GaussianRasterizer(settings)
+    loss_host = torch.zeros(1).pin_memory()
+    stats = {}
+
+    def step(src, grads_out=None):
+        leaves = {k: src[k].detach().requires_grad_(True) for k in LEAVES}
+        m2 = torch.zeros_like(leaves["means3D"], requires_grad=True)
+        color, radii = raster(means3D=leaves["means3D"], means2D=m2, opacities=leaves["opacities"], shs=leaves["sh"],
+                              scales=leaves["scales"], rotations=leaves["rotations"])
+        loss = (color * dpix).sum()
+        loss.backward()
+        grads = [leaves[k].grad for k in LEAVES]
+        if world > 1:  # per-Gaussian gradients of the replicated parameters: one NCCL all-reduce each (236 B/Gaussian)
+            work = [dist.all_reduce(g, async_op=True) for g in grads]
+            for w_ in work:
+                w_.wait()
+        stats["radii"] = radii
+        return loss, grads
+
+    def sync_all():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step(t)
+    sync_all()
+    # ---- timed region 1: inputs resident in HBM ("value"); per-stage device times recorded by the library
+    clocks = ClockSampler(local_rank) if rank == 0 else None
+    _lib.profile_enable(True)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(args.steps):
+        step(t)
+    b.record()
+    sync_all()
+    ms = a.elapsed_time(b) / args.steps
+    prof = _lib.profile_read()
+    _lib.profile_enable(False)
+    clk = clocks.stop() if clocks else None
+    # ---- timed region 2: end to end from pinned host buffers through the same public API
+    def e2e_step():
+        src = {k: host[k].to(dev, non_blocking=True) for k in LEAVES}
+        loss, _ = step(src)
+        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    for _ in range(2):
+        e2e_step()
+    sync_all()
+    a2, b2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n_e2e = max(3, args.steps // 2)
+    a2.record()
+    for _ in range(n_e2e):
+        e2e_step()
+    b2.record()
+    sync_all()
+    ms_e2e = a2.elapsed_time(b2) / n_e2e
+    if world > 1:
+        tt = torch.tensor([ms, ms_e2e], device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms, ms_e2e = float(tt[0]), float(tt[1])
+    if rank != 0:
+        return None
+    # ---- bookkeeping for the JSON line
+    radii = stats["radii"]
+    V = int((radii > 0).sum())
+    R = int(_lib_last_R(raster, t))
+    N = WIDTH * HEIGHT
+    K = (SH_DEG + 1) ** 2
+    a_total, a_stage = algorithmic_bytes(P_GAUSS, V, R, N, K, M_COEF)
+    peak, peak_kind = peaks()
+    per_stage_ms = {s: (v[0] / max(v[1], 1)) for s, v in prof.items()}
+    dom = max(a_stage, key=lambda s: per_stage_ms.get(s, 0.0))
+    dom_ms = per_stage_ms[dom]
+    achieved = a_stage[dom] / (dom_ms * 1e-3) / 1e9
+    kernels_per_step = 1 + 12 + 3 + 1 + 1 + 1 + 1
+    h2d = sum(host[k].numel() * 4 for k in LEAVES)
+    value = world * 1000.0 / ms
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "gaussians_per_s": value * P_GAUSS,
+        "config": {"workload": "C2: scene S (seed 0), 1M Gaussians, SH degree 3, 1920x1080, 1 view per GPU, fwd+bwd"
+                               + ("" if world == 1 else ", NCCL all-reduce of 236 B/Gaussian gradients"),
+                   "P": P_GAUSS, "visible": V, "num_rendered": R, "W": WIDTH, "H": HEIGHT,
+                   "l2": "inputs (236 MB) + scratch exceed the 126 MB L2; no explicit flush"},
+        "clocks": clk,
+        "e2e": {"value": world * 1000.0 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
+                "ms_per_step": ms_e2e},
+        "gpu_launches": kernels_per_step * args.steps,
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "peak_kind": peak_kind,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "algorithmic_bytes": a_stage[dom], "kernel_ms": dom_ms,
+                     "note": "alpha blending is FP32/MUFU-pipe bound, not HBM bound; the HBM fraction is reported "
+                             "because BASELINE.json's metric asks for it"},
+        "roofline_step": {"algorithmic_bytes": a_total, "achieved": a_total / (ms * 1e-3) / 1e9, "peak": peak,
+                          "unit": "GB/s", "frac": a_total / (ms * 1e-3) / 1e9 / peak},
+        "stage_ms": per_stage_ms,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(sc, dpix_np)
+    return line
+
+
+def _lib_last_R(raster, t):
+    """num_rendered of the benchmark view (one extra forward through the _C-shaped shim)."""
+    import torch
+    from diff_gaussian_rasterization import _C
+    e = torch.Tensor([])
+    s = raster.raster_settings
+    return _C.rasterize_gaussians(s.bg, t["means3D"], e, t["opacities"], t["scales"], t["rotations"], 1.0, e,
+                                  s.viewmatrix, s.projmatrix, s.tanfovx, s.tanfovy, s.image_height, s.image_width,
+                                  t["sh"], s.sh_degree, s.campos, False, False)[0]
+
+
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    if args.impl == "reference":
+        line = run_reference(args, rank, world)
+        if line is not None:
+            print(json.dumps(line), flush=True)
+        return
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a GPU (the product path has no CPU fallback)")
+    if world > 1:
+        import torch.distributed as dist
+        torch.cuda.set_device(local_rank)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    line = run_ours(args, rank, world, local_rank)
+    if line is not None:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -32,7 +32,7 @@
 namespace gsr {
 
 constexpr int BIN_WARPS = 4;           // warps per CTA in bin_pass
-constexpr int BAND_TILES_MAX = 4096;   // cursor-table entries per warp (16 KB)
+constexpr int BAND_TILES_MAX = 2048;   // cursor-table entries per warp (8 KB)
 
 struct BinPlan {
   int chunk;       // Gaussians per chunk (multiple of 32)
@@ -48,8 +48,9 @@ inline BinPlan make_bin_plan(int P, int gx, int gy) {
   p.chunk = chunk;
   p.n_chunks = P > 0 ? (P + chunk - 1) / chunk : 0;
   p.rows_per_band = BAND_TILES_MAX / gx;
-  if (p.rows_per_band < 1) p.rows_per_band = 0;  // image wider than 65536 px: unsupported, caller reports it
+  if (p.rows_per_band < 1) p.rows_per_band = 0;  // image wider than 32768 px: unsupported, caller reports it
   if (p.rows_per_band > gy) p.rows_per_band = gy;
+  if (p.rows_per_band > 1023) p.rows_per_band = 1023;  // row offsets travel in 10 bits of a packed shuffle word
   p.n_bands = p.rows_per_band ? (gy + p.rows_per_band - 1) / p.rows_per_band : 0;
   p.band_tiles = p.rows_per_band * gx;
   return p;
@@ -78,32 +79,39 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_pass_kernel(int P, const u
   const int begin = chunk * plan.chunk, end = min(P, begin + plan.chunk);
   for (int r0 = begin; r0 < end; r0 += 32) {
     const int k = r0 + lane;
-    uint32_t id = 0;
-    int minx = 0, maxx = 0, y0 = 0, y1 = 0;
+    uint32_t id = 0, w1 = 0, w2 = 0;  // w1 = x0 | width << 16 ; w2 = (y0 - by0) | height << 10 | magic << 20
+    bool has = false;
     if (k < end) {
       id = __ldg(order + k);
       const float4 a = __ldg(g0 + id);
       const int radius = __float_as_int(a.w);
       if (radius > 0) {
-        int miny, maxy;
+        int minx, miny, maxx, maxy;
         // same rectangle as duplicateWithKeys recomputes (rasterizer_impl.cu:85-90)
         get_rect(a.x, a.y, radius, gx, gy, minx, miny, maxx, maxy);
-        y0 = max(miny, by0);
-        y1 = min(maxy, by1);
+        const int y0 = max(miny, by0), y1 = min(maxy, by1);
+        has = (y1 > y0) && (maxx > minx);
+        if (has) {
+          const int wdt = maxx - minx;
+          // floor(t / wdt) == (t * magic) >> 10 for t < 32, wdt <= 32 (only used when the rect has <= 32 tiles)
+          const uint32_t magic = wdt <= 32 ? (1024u + wdt - 1u) / wdt : 0u;
+          w1 = (uint32_t)minx | ((uint32_t)wdt << 16);
+          w2 = (uint32_t)(y0 - by0) | ((uint32_t)(y1 - y0) << 10) | (magic << 20);  // magic <= 1024: 11 bits
+        }
       }
     }
-    unsigned live = __ballot_sync(0xffffffffu, (y1 > y0) && (maxx > minx));
+    unsigned live = __ballot_sync(0xffffffffu, has);
     while (live) {
       const int src = __ffs(live) - 1;
       live &= live - 1;
       const uint32_t gid = __shfl_sync(0xffffffffu, id, src);
-      const int x0 = __shfl_sync(0xffffffffu, minx, src), x1 = __shfl_sync(0xffffffffu, maxx, src);
-      const int ya = __shfl_sync(0xffffffffu, y0, src), yb = __shfl_sync(0xffffffffu, y1, src);
-      const int wdt = x1 - x0, nt = wdt * (yb - ya);
-      const int rowbase = (ya - by0) * gx + x0;
+      const uint32_t p1 = __shfl_sync(0xffffffffu, w1, src), p2 = __shfl_sync(0xffffffffu, w2, src);
+      const int x0 = p1 & 0xffff, wdt = p1 >> 16, ya = p2 & 0x3ff, hgt = (p2 >> 10) & 0x3ff;
+      const int nt = wdt * hgt;
+      const int rowbase = ya * gx + x0;
       if (nt <= 32) {
         if (lane < nt) {
-          const int ty = __float2int_rz(((float)lane + 0.5f) * __frcp_rn((float)wdt));  // exact for lane, wdt <= 32
+          const int ty = (int)(((uint32_t)lane * (p2 >> 20)) >> 10);
           const int idx = rowbase + ty * gx + (lane - ty * wdt);
           const uint32_t v = tab[idx];
           tab[idx] = v + 1u;
@@ -128,13 +136,13 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_pass_kernel(int P, const u
 }
 
 // matrix[chunk][tile] -> exclusive prefix over chunks (in place); tile_count[tile] = column total.
-// CTA = 32 tiles x 8 chunk groups.
-__global__ void __launch_bounds__(256) column_scan_kernel(uint32_t* __restrict__ matrix, int n_chunks, int T,
+// CTA = 32 tiles x 32 chunk groups.
+__global__ void __launch_bounds__(1024) column_scan_kernel(uint32_t* __restrict__ matrix, int n_chunks, int T,
                                                           uint32_t* __restrict__ tile_count) {
-  __shared__ uint32_t part[8][33];
+  __shared__ uint32_t part[32][33];
   const int tx = threadIdx.x & 31, g = threadIdx.x >> 5;
   const int tile = blockIdx.x * 32 + tx;
-  const int per = (n_chunks + 7) / 8;
+  const int per = (n_chunks + 31) / 32;
   const int c0 = min(n_chunks, g * per), c1 = min(n_chunks, c0 + per);
   uint32_t sum = 0;
   if (tile < T)
@@ -150,7 +158,7 @@ __global__ void __launch_bounds__(256) column_scan_kernel(uint32_t* __restrict__
       matrix[i] = run;
       run += v;
     }
-    if (g == 7) tile_count[tile] = run;
+    if (g == 31) tile_count[tile] = run;
   }
 }
 

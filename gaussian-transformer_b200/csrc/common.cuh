@@ -39,7 +39,7 @@ __host__ __device__ inline size_t align_up(size_t v) { return (v + ALIGN - 1) & 
 //   g1 float4[P]  conic.x, conic.y, conic.z, opacity
 //   g2 float4[P]  r, g, b, flags (bits 0..2 = clamped r/g/b, bits 3.. = tiles_touched)
 //   keys[2] u32[P], vals[2] u32[P]  depth-sort ping-pong (keys = depth bits, 0xffffffff for culled)
-//   cta_hist u32[256 * n_sort_cta]  radix digit histograms
+//   cta_hist u32[256 * n_sort_cta + 256]  radix digit histograms (digit-major) + digit totals
 // image
 //   final_T f32[N], n_contrib u32[N], ranges uint2[T], tile_count u32[T], ctrl u32[64],
 //   matrix u32[n_chunks * T] (binning.cuh)
@@ -83,7 +83,7 @@ inline size_t bin_chunks(size_t P) {  // must match make_bin_plan (binning.cuh)
 }
 
 inline size_t geom_bytes(size_t P) {
-  return 3 * align_up(16 * P) + 4 * align_up(4 * P) + align_up(4 * 256 * sort_ctas(P)) + ALIGN;
+  return 3 * align_up(16 * P) + 4 * align_up(4 * P) + align_up(4 * 256 * (sort_ctas(P) + 1)) + ALIGN;
 }
 inline GeomView geom_view(void* base, size_t P) {
   char* p = (char*)base;

@@ -9,8 +9,8 @@
 // tile part is resolved afterwards by an order-preserving binning pass
 // (binning.cuh) that needs no keys at all.
 //
-// Per pass: (A) per-CTA digit histogram, (B) one-CTA exclusive scan over the
-// digit-major histogram matrix, (C) stable scatter.  In (C) every warp owns a
+// Per pass: (A) per-CTA digit histogram, (B) per-digit row scan of the
+// digit-major histogram matrix (256 CTAs), (C) stable scatter.  In (C) every warp owns a
 // contiguous 512-key segment of the CTA's 4096-key tile, keeps it in registers,
 // ranks keys with match.any against per-warp digit counters in shared memory
 // and writes them to their final position.
@@ -40,46 +40,37 @@ __global__ void __launch_bounds__(RS_THREADS) radix_hist_kernel(const uint32_t* 
   cta_hist[(size_t)threadIdx.x * n_cta + blockIdx.x] = h[threadIdx.x];
 }
 
-// In-place exclusive scan of n u32 values by ONE CTA of 1024 threads (n up to a few million).
-// If total_out != nullptr the grand total (64-bit) is written there as two u32 words.
-__global__ void __launch_bounds__(1024) exclusive_scan_kernel(uint32_t* __restrict__ data, int n,
-                                                              uint32_t* __restrict__ total_out) {
-  __shared__ unsigned long long warp_tot[32];
-  __shared__ unsigned long long carry_s;
+// One CTA per digit d: in-place exclusive scan of row d of the digit-major matrix cta_hist[256][n_cta]
+// (the position, among keys with digit d, of the first such key of each CTA tile); digit_total[d] = row sum.
+__global__ void __launch_bounds__(256) radix_rowscan_kernel(uint32_t* __restrict__ cta_hist, int n_cta,
+                                                            uint32_t* __restrict__ digit_total) {
+  __shared__ uint32_t warp_tot[8];
+  __shared__ uint32_t carry_s;
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
-  if (tid == 0) carry_s = 0ull;
+  uint32_t* row = cta_hist + (size_t)blockIdx.x * n_cta;
+  if (tid == 0) carry_s = 0u;
   __syncthreads();
-  for (int base = 0; base < n; base += 1024) {
+  for (int base = 0; base < n_cta; base += 256) {
     const int i = base + tid;
-    const uint32_t c = i < n ? data[i] : 0u;
-    unsigned long long v = c;
+    const uint32_t c = i < n_cta ? row[i] : 0u;
+    uint32_t v = c;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-      const unsigned long long t = __shfl_up_sync(0xffffffffu, v, o);
+      const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
       if (lane >= o) v += t;
     }
     if (lane == 31) warp_tot[wid] = v;
     __syncthreads();
-    if (wid == 0) {
-      unsigned long long w = warp_tot[lane];
+    uint32_t pre = carry_s;
 #pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const unsigned long long t = __shfl_up_sync(0xffffffffu, w, o);
-        if (lane >= o) w += t;
-      }
-      warp_tot[lane] = w;
-    }
+    for (int k = 0; k < 8; k++)
+      if (k < wid) pre += warp_tot[k];
+    if (i < n_cta) row[i] = pre + v - c;
     __syncthreads();
-    const unsigned long long incl = carry_s + v + (wid > 0 ? warp_tot[wid - 1] : 0ull);
-    if (i < n) data[i] = (uint32_t)(incl - c);
-    __syncthreads();
-    if (tid == 1023) carry_s = incl;
+    if (tid == 255) carry_s = pre + v;
     __syncthreads();
   }
-  if (tid == 0 && total_out) {
-    total_out[0] = (uint32_t)(carry_s & 0xffffffffull);
-    total_out[1] = (uint32_t)(carry_s >> 32);
-  }
+  if (tid == 0) digit_total[blockIdx.x] = carry_s;
 }
 
 // vals_in == nullptr means "identity" (value = index), used by the first pass.
@@ -87,9 +78,11 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
                                                                    const uint32_t* __restrict__ vals_in, int n,
                                                                    int shift, int n_cta,
                                                                    const uint32_t* __restrict__ cta_offs,
+                                                                   const uint32_t* __restrict__ digit_total,
                                                                    uint32_t* __restrict__ keys_out,
                                                                    uint32_t* __restrict__ vals_out) {
   __shared__ uint32_t cnt[RS_WARPS][256];  // per-warp digit counts, then per-warp running output positions
+  __shared__ uint32_t dbase[256];          // exclusive scan of digit_total
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   for (int k = tid; k < RS_WARPS * 256; k += RS_THREADS) (&cnt[0][0])[k] = 0u;
   __syncthreads();
@@ -112,10 +105,27 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
     __syncwarp();
   }
   __syncthreads();
+  // exclusive scan of the 256 digit totals (every CTA redoes it: 256 values)
+  {
+    const uint32_t c = __ldg(digit_total + tid);
+    uint32_t v = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+      if (lane >= o) v += t;
+    }
+    dbase[tid] = v;  // inclusive within the warp's 32 digits
+    __syncthreads();
+    uint32_t pre = 0;
+    for (int ww = 0; ww < w; ww++) pre += dbase[ww * 32 + 31];
+    __syncthreads();
+    dbase[tid] = pre + v - c;
+    __syncthreads();
+  }
   // per digit: exclusive prefix over the warps + this CTA's global offset
   {
     const int d = tid;  // RS_THREADS == 256 digits
-    uint32_t run = __ldg(cta_offs + (size_t)d * n_cta + blockIdx.x);
+    uint32_t run = dbase[d] + __ldg(cta_offs + (size_t)d * n_cta + blockIdx.x);
 #pragma unroll
     for (int ww = 0; ww < RS_WARPS; ww++) {
       const uint32_t c = cnt[ww][d];

@@ -1,11 +1,14 @@
 // csrc/gsrast_api.cu -- the C ABI of libgsrast.so (see include/gsrast.h) and the
 // host-side orchestration of the kernels.  Stateless: no globals besides a
-// thread-local error string; no device allocation.
+// thread-local error string and the opt-in profiler; no device allocation.
 #include <cuda_runtime.h>
 
 #include <cstdio>
 #include <cstring>
+#include <atomic>
+#include <mutex>
 #include <string>
+#include <vector>
 
 #include "../../include/gsrast.h"
 #include "binning.cuh"
@@ -49,6 +52,44 @@ int cuda_fail(cudaError_t e, const char* where) {
       if (e__ != cudaSuccess) return cuda_fail(e__, name);              \
     }                                                                   \
   } while (0)
+
+// ---- optional per-stage device timing (gsr_profile_*): process-wide (autograd runs backward on its own
+// thread), mutex-protected, off by default
+struct StageSpan { int stage; cudaEvent_t a, b; };
+struct Profiler {
+  std::atomic<bool> on{false};
+  std::mutex mu;
+  std::vector<StageSpan> spans;
+  std::vector<cudaEvent_t> pool;
+  cudaEvent_t get() {
+    if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+    cudaEvent_t e = nullptr;
+    cudaEventCreate(&e);
+    return e;
+  }
+};
+Profiler g_prof;
+struct ScopedStage {
+  bool live;
+  cudaStream_t st;
+  StageSpan sp;
+  ScopedStage(int stage, cudaStream_t s) : live(g_prof.on.load()), st(s) {
+    if (!live) return;
+    sp.stage = stage;
+    {
+      std::lock_guard<std::mutex> lk(g_prof.mu);
+      sp.a = g_prof.get();
+      sp.b = g_prof.get();
+    }
+    cudaEventRecord(sp.a, st);
+  }
+  ~ScopedStage() {
+    if (!live) return;
+    cudaEventRecord(sp.b, st);
+    std::lock_guard<std::mutex> lk(g_prof.mu);
+    g_prof.spans.push_back(sp);
+  }
+};
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
@@ -100,6 +141,28 @@ extern "C" {
 int gsr_version(void) { return 100; }
 int gsr_compiled_arch(void) { return 100; }
 const char* gsr_last_error(void) { return g_err.c_str(); }
+
+int gsr_profile_enable(int on) {
+  g_prof.on.store(on != 0);
+  return GSR_OK;
+}
+
+int gsr_profile_read(float* ms, int32_t* counts) {
+  if (!ms || !counts) return fail(GSR_ERR_INVALID, "gsr_profile_read: NULL output");
+  for (int k = 0; k < GSR_STAGE_COUNT; k++) { ms[k] = 0.f; counts[k] = 0; }
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  for (const StageSpan& sp : g_prof.spans) {
+    GSR_CUDA(cudaEventSynchronize(sp.b), "profile event sync");
+    float t = 0.f;
+    GSR_CUDA(cudaEventElapsedTime(&t, sp.a, sp.b), "profile elapsed");
+    ms[sp.stage] += t;
+    counts[sp.stage] += 1;
+    g_prof.pool.push_back(sp.a);
+    g_prof.pool.push_back(sp.b);
+  }
+  g_prof.spans.clear();
+  return GSR_OK;
+}
 
 int gsr_scratch_bytes(int32_t P, int64_t R, int32_t W, int32_t H, size_t* geom, size_t* binning, size_t* image,
                       size_t* bwd) {
@@ -167,12 +230,14 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   GeomView g = geom_view(geom, (size_t)in->P);
   ImageView im = image_view(image, N, T);
   const BinPlan plan = make_bin_plan(in->P, cam.gx, cam.gy);
-  if (plan.n_bands == 0) return fail(GSR_ERR_INVALID, "image wider than 65536 pixels is not supported");
+  if (plan.n_bands == 0) return fail(GSR_ERR_INVALID, "image wider than 32768 pixels is not supported");
   GSR_CUDA(cudaMemsetAsync(im.ctrl, 0, 4 * CTRL_WORDS, stream), "memset ctrl");
   const int K = (in->D + 1) * (in->D + 1);
   const bool vec_sh = in->sh && !in->colors_precomp && ((K * 3) % 4 == 0) && ((in->M * 12) % 16 == 0) &&
                       aligned16(in->sh);
   const int blocks = (in->P + 255) / 256;
+  {
+  ScopedStage prof_(GSR_STAGE_PREPROCESS_FWD, stream);
   if (vec_sh)
     preprocess_fwd_kernel<true><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
                                                             in->rotations, in->opacities, in->sh,
@@ -184,16 +249,24 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
                                                              in->colors_precomp, in->cov3D_precomp, cam,
                                                              in->prefiltered, radii, g, im.ctrl);
   GSR_STAGE("preprocess_fwd", in->debug, stream);
+  }
   // depth sort of the P Gaussians: 4 stable 8-bit passes, result in keys[0] / vals[0]
   const int n_cta = (int)sort_ctas((size_t)in->P);
+  {
+  ScopedStage prof_(GSR_STAGE_DEPTH_SORT, stream);
   for (int pass = 0; pass < 4; pass++) {
     const int src = pass & 1, dst = src ^ 1, shift = 8 * pass;
     radix_hist_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], in->P, shift, n_cta, g.cta_hist);
-    exclusive_scan_kernel<<<1, 1024, 0, stream>>>(g.cta_hist, 256 * n_cta, nullptr);
+    uint32_t* digit_total = g.cta_hist + (size_t)256 * n_cta;
+    radix_rowscan_kernel<<<256, 256, 0, stream>>>(g.cta_hist, n_cta, digit_total);
     radix_scatter_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], pass == 0 ? nullptr : g.vals[src], in->P,
-                                                          shift, n_cta, g.cta_hist, g.keys[dst], g.vals[dst]);
+                                                          shift, n_cta, g.cta_hist, digit_total, g.keys[dst],
+                                                          g.vals[dst]);
     GSR_STAGE("depth_sort", in->debug, stream);
   }
+  }
+  {
+  ScopedStage prof_(GSR_STAGE_BIN_COUNT, stream);
   // order-preserving binning, counting half
   const int tasks = plan.n_chunks * plan.n_bands;
   const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
@@ -202,10 +275,11 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   bin_pass_kernel<false><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
       in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, nullptr);
   GSR_STAGE("bin_count", in->debug, stream);
-  column_scan_kernel<<<((int)T + 31) / 32, 256, 0, stream>>>(im.matrix, plan.n_chunks, (int)T, im.tile_count);
+  column_scan_kernel<<<((int)T + 31) / 32, 1024, 0, stream>>>(im.matrix, plan.n_chunks, (int)T, im.tile_count);
   GSR_STAGE("column_scan", in->debug, stream);
   tile_scan_kernel<<<1, 1024, 0, stream>>>((int)T, im.tile_count, im.ranges, im.ctrl);
   GSR_STAGE("tile_scan", in->debug, stream);
+  }
   // ctrl[CTRL_R_LO..HI] -> host_result[0] (little endian int64), flags -> [1]
   GSR_CUDA(cudaMemcpyAsync(&host_result[0], im.ctrl + CTRL_R_LO, 8, cudaMemcpyDeviceToHost, stream), "copy R");
   GSR_CUDA(cudaMemcpyAsync(&host_result[1], im.ctrl + CTRL_FLAGS, 4, cudaMemcpyDeviceToHost, stream), "copy flags");
@@ -232,6 +306,7 @@ int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void
   ImageView im = image_view(image, N, T);
   BinView b = bin_view(binning, (size_t)R);
   if (R > 0) {
+    ScopedStage prof_(GSR_STAGE_BIN_SCATTER, stream);
     const BinPlan plan = make_bin_plan(in->P, cam.gx, cam.gy);
     const int tasks = plan.n_chunks * plan.n_bands;
     const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
@@ -241,6 +316,7 @@ int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void
         in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list);
     GSR_STAGE("bin_scatter", in->debug, stream);
   }
+  ScopedStage prof_(GSR_STAGE_RENDER_FWD, stream);
   dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
   render_fwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, g.g0, g.g1, g.g2,
                                                 in->colors_precomp, in->bg, im.final_T, im.n_contrib, out_color);
@@ -271,6 +347,7 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
   BwdView bw = bwd_view(bwd_scratch, (size_t)in->P);
   GSR_CUDA(cudaMemsetAsync(bwd_scratch, 0, bwd_bytes((size_t)in->P), stream), "memset bwd accumulators");
   if (R > 0) {
+    ScopedStage prof_(GSR_STAGE_RENDER_BWD, stream);
     dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
     render_bwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0, g.g1, g.g2,
                                                   in->colors_precomp, im.final_T, im.n_contrib, dL_dpix, bw.acc);
@@ -286,6 +363,7 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
   out.dL_drot = dL_drotations;
   out.dL_dcov3D = dL_dcov3D;
   out.dL_dconic = dL_dconic;
+  ScopedStage prof_(GSR_STAGE_PREPROCESS_BWD, stream);
   preprocess_bwd_kernel<<<(in->P + 255) / 256, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
                                                                 in->rotations, in->sh, in->cov3D_precomp, cam,
                                                                 radii, g.g2, bw.acc, out);

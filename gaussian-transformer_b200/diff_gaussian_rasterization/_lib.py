@@ -32,8 +32,9 @@ class gsr_views(ctypes.Structure):
 # every symbol include/gsrast.h declares
 EXPORTS = (
     "gsr_version", "gsr_compiled_arch", "gsr_last_error", "gsr_scratch_bytes", "gsr_forward_pre",
-    "gsr_forward_post", "gsr_backward", "gsr_mark_visible", "gsr_get_views",
+    "gsr_forward_post", "gsr_backward", "gsr_mark_visible", "gsr_get_views", "gsr_profile_enable", "gsr_profile_read",
 )
+STAGES = ("preprocess_fwd", "depth_sort", "bin_count", "bin_scatter", "render_fwd", "render_bwd", "preprocess_bwd")
 
 
 def load(path=LIB_PATH):
@@ -54,7 +55,9 @@ def load(path=LIB_PATH):
     lib.gsr_backward.argtypes = [inp, vp, vp, vp, vp, i64, vp] + [vp] * 9 + [vp, vp]
     lib.gsr_mark_visible.argtypes = [i32, vp, vp, vp, vp, vp]
     lib.gsr_get_views.argtypes = [i32, i64, i32, i32, vp, vp, vp, ctypes.POINTER(gsr_views)]
-    for name in ("gsr_scratch_bytes", "gsr_forward_pre", "gsr_forward_post", "gsr_backward", "gsr_mark_visible",
+    lib.gsr_profile_enable.argtypes = [ctypes.c_int]
+    lib.gsr_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int32)]
+    for name in ("gsr_profile_enable", "gsr_profile_read", "gsr_scratch_bytes", "gsr_forward_pre", "gsr_forward_post", "gsr_backward", "gsr_mark_visible",
                  "gsr_get_views"):
         getattr(lib, name).restype = ctypes.c_int
     return lib
@@ -73,3 +76,15 @@ def scratch_bytes(P, R, W, H):
     g, b, i, w = (ctypes.c_size_t() for _ in range(4))
     check(lib.gsr_scratch_bytes(P, R, W, H, ctypes.byref(g), ctypes.byref(b), ctypes.byref(i), ctypes.byref(w)))
     return g.value, b.value, i.value, w.value
+
+
+def profile_enable(on=True):
+    check(lib.gsr_profile_enable(int(on)))
+
+
+def profile_read():
+    """-> {stage: (total_ms, launches)} accumulated on this thread since the previous read."""
+    ms = (ctypes.c_float * len(STAGES))()
+    n = (ctypes.c_int32 * len(STAGES))()
+    check(lib.gsr_profile_read(ms, n))
+    return {s: (float(ms[i]), int(n[i])) for i, s in enumerate(STAGES)}

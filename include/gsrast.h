@@ -142,6 +142,24 @@ GSR_API int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void*
 GSR_API int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
                      const float* projmatrix, uint8_t* present, void* stream);
 
+/* Optional per-stage device timing (used by bench.py for the roofline numbers; the reference has no counterpart
+ * beyond the CUDA-event pair of train.py:44-45).  Process-wide (autograd runs backward on its own thread), mutex
+ * protected, off by default.  While enabled, every call brackets each stage with CUDA events on the caller's stream (no synchronisation);
+ * gsr_profile_read synchronises those events, returns per-stage total milliseconds and launch counts accumulated
+ * since the previous read, and recycles the events. */
+enum {
+  GSR_STAGE_PREPROCESS_FWD = 0, /* preprocess_fwd_kernel */
+  GSR_STAGE_DEPTH_SORT = 1,     /* 4 x (radix_hist, exclusive_scan, radix_scatter) */
+  GSR_STAGE_BIN_COUNT = 2,      /* bin_pass<count>, column_scan, tile_scan */
+  GSR_STAGE_BIN_SCATTER = 3,    /* bin_pass<scatter> */
+  GSR_STAGE_RENDER_FWD = 4,     /* render_fwd_kernel */
+  GSR_STAGE_RENDER_BWD = 5,     /* render_bwd_kernel */
+  GSR_STAGE_PREPROCESS_BWD = 6, /* preprocess_bwd_kernel */
+  GSR_STAGE_COUNT = 7
+};
+GSR_API int gsr_profile_enable(int on);
+GSR_API int gsr_profile_read(float* ms /* [GSR_STAGE_COUNT] */, int32_t* counts /* [GSR_STAGE_COUNT] */);
+
 /* Decoded views into the scratch buffers of a finished forward (device
  * pointers into geom / image / binning) -- the counterpart of
  * GeometryState / ImageState / BinningState::fromChunk
