@@ -46,7 +46,9 @@ __host__ __device__ inline size_t align_up(size_t v) { return (v + ALIGN - 1) & 
 // binning
 //   point_list u32[R] (depth-sorted gaussian ids, tile after tile)
 // bwd
-//   acc float[P][12]: dL_dcolor.rgb, dL_dopacity, dL_dmean2D.xy, dL_dconic.xx, .xy, .yy, 3 unused
+//   acc0 float4[P]: dL_dcolor.rgb, dL_dopacity;  acc1 float4[P]: dL_dmean2D.xy, dL_dconic.xx, .xy;
+//   acc2 float[P]: dL_dconic.yy   (SoA so that preprocess_bwd reads them with coalesced 128-bit loads).
+//   acc1 / acc2 hold the sums WITHOUT their per-Gaussian constant factors; finish_2d_grads() applies them.
 struct GeomView {
   float4* g0;
   float4* g1;
@@ -67,7 +69,9 @@ struct BinView {
   uint32_t* point_list;
 };
 struct BwdView {
-  float* acc;
+  float4* acc0;
+  float4* acc1;
+  float* acc2;
 };
 
 // ctrl[] slots
@@ -120,11 +124,13 @@ inline BinView bin_view(void* base, size_t R) {
   v.point_list = (uint32_t*)base;
   return v;
 }
-inline size_t bwd_bytes(size_t P) { return align_up(48 * P) + ALIGN; }
+inline size_t bwd_bytes(size_t P) { return 2 * align_up(16 * P) + align_up(4 * P) + ALIGN; }
 inline BwdView bwd_view(void* base, size_t P) {
-  (void)P;
+  char* p = (char*)base;
   BwdView v;
-  v.acc = (float*)base;
+  v.acc0 = (float4*)p; p += align_up(16 * P);
+  v.acc1 = (float4*)p; p += align_up(16 * P);
+  v.acc2 = (float*)p;
   return v;
 }
 
@@ -190,6 +196,17 @@ __device__ __forceinline__ float warp_sum(float v) {
   v += __shfl_xor_sync(0xffffffffu, v, 2);
   v += __shfl_xor_sync(0xffffffffu, v, 1);
   return v;
+}
+
+// render_bwd accumulates  sum q*(dx A + dy B), sum q*(dx B + dy C), sum q dx dx, sum q dx dy, sum q dy dy  with
+// q = G * dL/dalpha; the reference's 2-D gradients (backward.cu:541-551) are these times per-Gaussian constants.
+__device__ __forceinline__ void finish_2d_grads(float opacity, int W, int H, float4& B, float& Cyy) {
+  const float mo = -opacity;
+  B.x *= mo * (0.5f * W);
+  B.y *= mo * (0.5f * H);
+  B.z *= 0.5f * mo;
+  B.w *= 0.5f * mo;
+  Cyy *= 0.5f * mo;
 }
 
 // Vector float atomics (sm_90+): one RED for four consecutive floats.

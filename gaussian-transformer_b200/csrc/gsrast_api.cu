@@ -337,8 +337,6 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
       !dL_dcov3D || !dL_dconic)
     return fail(GSR_ERR_INVALID, "gsr_backward: NULL gradient output");
   if (in->sh && in->M > 0 && !dL_dsh) return fail(GSR_ERR_INVALID, "gsr_backward: dL_dsh is NULL");
-  if (!aligned16(dL_drotations) || !aligned16(dL_dconic))
-    return fail(GSR_ERR_INVALID, "dL_drotations / dL_dconic must be 16-byte aligned");
   const Cam cam = make_cam(in);
   const size_t N = (size_t)in->W * in->H, T = (size_t)cam.gx * cam.gy;
   GeomView g = geom_view(const_cast<void*>(geom), (size_t)in->P);
@@ -350,7 +348,7 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
     ScopedStage prof_(GSR_STAGE_RENDER_BWD, stream);
     dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
     render_bwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0, g.g1, g.g2,
-                                                  in->colors_precomp, im.final_T, im.n_contrib, dL_dpix, bw.acc);
+                                                  in->colors_precomp, im.final_T, im.n_contrib, dL_dpix, bw);
     GSR_STAGE("render_bwd", in->debug, stream);
   }
   BwdOut out;
@@ -364,9 +362,27 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
   out.dL_dcov3D = dL_dcov3D;
   out.dL_dconic = dL_dconic;
   ScopedStage prof_(GSR_STAGE_PREPROCESS_BWD, stream);
-  preprocess_bwd_kernel<<<(in->P + 255) / 256, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
-                                                                in->rotations, in->sh, in->cov3D_precomp, cam,
-                                                                radii, g.g2, bw.acc, out);
+  // staged (coalesced) variant: SH rows of 16 or 4 coefficients and 16-byte aligned arrays; else the generic one
+  const bool staged = in->sh && out.dL_dsh && (in->M == 16 || in->M == 4) && aligned16(in->sh) &&
+                      aligned16(dL_dsh) && aligned16(dL_dmeans3D) && aligned16(dL_dmeans2D) &&
+                      aligned16(dL_dcolors) && aligned16(dL_dscales) && aligned16(dL_dcov3D) &&
+                      aligned16(dL_dconic) && aligned16(dL_drotations);
+  const int pb_blocks = (in->P + PB_THREADS - 1) / PB_THREADS;
+  if (staged && in->M == 16) {
+    const int smem = PB_THREADS * 13 * 16;
+    preprocess_bwd_staged_kernel<16><<<pb_blocks, PB_THREADS, smem, stream>>>(
+        in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, in->cov3D_precomp, cam, radii,
+        g.g2, bw, out);
+  } else if (staged) {
+    const int smem = PB_THREADS * 3 * 16;
+    preprocess_bwd_staged_kernel<4><<<pb_blocks, PB_THREADS, smem, stream>>>(
+        in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, in->cov3D_precomp, cam, radii,
+        g.g2, bw, out);
+  } else {
+    preprocess_bwd_kernel<<<pb_blocks, PB_THREADS, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
+                                                                in->rotations, g.g1, in->sh, in->cov3D_precomp,
+                                                                cam, radii, g.g2, bw, out);
+  }
   GSR_STAGE("preprocess_bwd", in->debug, stream);
   return GSR_OK;
 }

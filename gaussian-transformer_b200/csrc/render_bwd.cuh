@@ -9,17 +9,16 @@
 //   * the 9 partial gradients of a Gaussian are summed across the warp with a
 //     reduce-scatter butterfly: 12 shuffles instead of 45, after which 9 lanes
 //     each hold one finished sum;
-//   * those 9 lanes issue ONE predicated RED instruction into a 48-byte
-//     per-Gaussian accumulator row (9 floats used), i.e. one atomic instruction
-//     per (warp, Gaussian) instead of 9 per (pixel, Gaussian).
+//   * those 9 lanes issue ONE predicated RED instruction into the per-Gaussian
+//     accumulators (common.cuh BwdView: two float4 arrays + one float array),
+//     i.e. one atomic instruction per (warp, Gaussian) instead of 9 per
+//     (pixel, Gaussian).
 #pragma once
 #include "common.cuh"
 #include "cull.cuh"
 #include "render_fwd.cuh"
 
 namespace gsr {
-
-constexpr int ACC_STRIDE = 12;  // floats per Gaussian in the accumulator array (9 used)
 
 // pair step of the reduce-scatter: lanes with `hi` clear end up with sum(a), lanes with it set with sum(b)
 __device__ __forceinline__ float rs_pair(float a, float b, bool hi, int xorm) {
@@ -52,9 +51,9 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
                                                          const float* __restrict__ colors_precomp,
                                                          const float* __restrict__ final_T,
                                                          const uint32_t* __restrict__ n_contrib,
-                                                         const float* __restrict__ dL_dpix, float* __restrict__ acc) {
+                                                         const float* __restrict__ dL_dpix, BwdView acc) {
   __shared__ StageRec s_rec[RENDER_BATCH];
-  __shared__ uint32_t s_pos[RENDER_BATCH];
+  __shared__ float s_rba[RENDER_BATCH];
   __shared__ uint32_t s_id[RENDER_BATCH];
   __shared__ int s_warp[8];
   __shared__ uint32_t s_maxc;
@@ -70,6 +69,8 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
   if (range.y == range.x) return;
   const size_t N = (size_t)W * H, pix = (size_t)pix_y * W + pix_x;
+  const uint32_t rec_addr = smem_addr(s_rec);
+  const uint32_t id_addr = smem_addr(s_id);
 
   const float T_final = inside ? final_T[pix] : 0.f;
   float T = T_final;
@@ -81,8 +82,8 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
     dLp2 = dL_dpix[2 * N + pix];
   }
   const float bg_dot = __ldg(bg) * dLp0 + __ldg(bg + 1) * dLp1 + __ldg(bg + 2) * dLp2;
-  float acr0 = 0.f, acr1 = 0.f, acr2 = 0.f, lc0 = 0.f, lc1 = 0.f, lc2 = 0.f, last_alpha = 0.f;
-  const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+  const float tfinal_bg = T_final * bg_dot;
+  float S = 0.f, lcd = 0.f, last_alpha = 0.f;
 
   // list entries behind every pixel's last contributor are never touched
   uint32_t wmax = last_contributor;
@@ -96,68 +97,74 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
   // which accumulator slot this lane commits after the reduce-scatter (-1: none)
   const int commit = ((lane & 3) == 0) ? (((lane >> 2) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 4) & 1))
                                        : (lane == 2 ? 8 : -1);
+  float* const commit_base = commit < 0 ? nullptr
+                             : commit < 4 ? reinterpret_cast<float*>(acc.acc0) + commit
+                             : commit < 8 ? reinterpret_cast<float*>(acc.acc1) + (commit - 4)
+                                          : acc.acc2;
+  const uint32_t commit_shift = commit == 8 ? 0u : 2u;  // element offset of Gaussian id = id << shift (P < 2^29)
 
   for (int start = 0; start < n_eff; start += RENDER_BATCH) {
     __syncthreads();  // previous batch fully consumed before it is overwritten
     const int n_batch = min(RENDER_BATCH, n_eff - start);
     const int first = n_eff - 1 - start;
     const int cnt = stage_batch(tid, n_batch, point_list + range.x + first, -1, first, g0, g1, g2, colors_precomp,
-                                tx0, ty0, s_rec, s_pos, s_id, s_warp);
+                                tx0, ty0, s_rec, s_rba, s_id, s_warp);
     for (int c0 = 0; c0 < cnt; c0 += 32) {
       bool hit = false;
-      if (c0 + lane < cnt && s_pos[c0 + lane] < wmax) {
+      if (c0 + lane < cnt && __float_as_uint(s_rec[c0 + lane].c.w) < wmax) {
         const float4 a = s_rec[c0 + lane].a, b = s_rec[c0 + lane].b;
         CullPre pre;
-        pre.thr = b.z; pre.rBC = b.w; pre.rBA = s_rec[c0 + lane].c.w;
+        pre.thr = b.z; pre.rBC = b.w; pre.rBA = s_rba[c0 + lane];
         hit = !cull_rect(a.x, a.y, a.z, a.w, b.x, pre, wx0, wx0 + 7.f, wy0, wy0 + 3.f);
       }
       unsigned mask = __ballot_sync(0xffffffffu, hit);
+      const uint32_t chunk_addr = rec_addr + (uint32_t)c0 * (uint32_t)sizeof(StageRec);
+      const uint32_t chunk_id_addr = id_addr + (uint32_t)c0 * 4u;
       while (mask) {
-        const int j = c0 + __ffs(mask) - 1;
+        const uint32_t bit = (uint32_t)(__ffs(mask) - 1);
         mask &= mask - 1;
-        const float4 a = s_rec[j].a, b = s_rec[j].b;
-        bool valid = s_pos[j] < last_contributor;
-        float G = 0.f, alpha = 0.f;
+        const uint32_t addr = chunk_addr + bit * (uint32_t)sizeof(StageRec);
+        const float4 a = lds128(addr);
+        const float2 b = lds64(addr + 16);
+        const float4 col = lds128(addr + 32);
         const float dx = __fsub_rn(a.x, pfx), dy = __fsub_rn(a.y, pfy);
-        if (valid) {
-          const float power = gauss_power(dx, dy, a.z, a.w, b.x);
-          valid = !(power > 0.0f);
-          if (valid) {
-            G = expf(power);
-            alpha = fminf(0.99f, __fmul_rn(b.y, G));
-            valid = !(alpha < 1.0f / 255.0f);
-          }
-        }
+        const float power = gauss_power(dx, dy, a.z, a.w, b.x);
+        const float G = expf(power);
+        const float alpha = fminf(0.99f, __fmul_rn(b.y, G));
+        // same acceptance as the forward (backward.cu:488-497): behind the last contributor, power > 0 and
+        // alpha < 1/255 are skipped
+        const bool valid = (__float_as_uint(col.w) < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
         if (!__any_sync(0xffffffffu, valid)) continue;
-        float v0 = 0.f, v1 = 0.f, v2 = 0.f, v3 = 0.f, v4 = 0.f, v5 = 0.f, v6 = 0.f, v7 = 0.f, v8 = 0.f;
-        if (valid) {
-          T = T / (1.f - alpha);
-          const float dchannel_dcolor = alpha * T;
-          const float4 col = s_rec[j].c;
-          acr0 = last_alpha * lc0 + (1.f - last_alpha) * acr0;
-          acr1 = last_alpha * lc1 + (1.f - last_alpha) * acr1;
-          acr2 = last_alpha * lc2 + (1.f - last_alpha) * acr2;
-          lc0 = col.x; lc1 = col.y; lc2 = col.z;
-          float dL_dalpha = (col.x - acr0) * dLp0 + (col.y - acr1) * dLp1 + (col.z - acr2) * dLp2;
-          v0 = dchannel_dcolor * dLp0;
-          v1 = dchannel_dcolor * dLp1;
-          v2 = dchannel_dcolor * dLp2;
-          dL_dalpha *= T;
-          last_alpha = alpha;
-          dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot;
-          const float dL_dG = b.y * dL_dalpha;
-          const float gdx = G * dx, gdy = G * dy;
-          const float dG_ddelx = -gdx * a.z - gdy * a.w;
-          const float dG_ddely = -gdy * b.x - gdx * a.w;
-          v3 = G * dL_dalpha;                // dL_dopacity
-          v4 = dL_dG * dG_ddelx * ddelx_dx;  // dL_dmean2D.x
-          v5 = dL_dG * dG_ddely * ddely_dy;  // dL_dmean2D.y
-          v6 = -0.5f * gdx * dx * dL_dG;     // dL_dconic.xx
-          v7 = -0.5f * gdx * dy * dL_dG;     // dL_dconic.xy
-          v8 = -0.5f * gdy * dy * dL_dG;     // dL_dconic.yy
-        }
+        // Predicated body.  Algebra relative to backward.cu:499-554 (results identical up to rounding):
+        //  * the pixel's dL/dpixel is constant over the list, so the reference's three accumulated colours enter
+        //    only through their dot product with it: S = <accum_rec, dLp> obeys the same linear recurrence;
+        //  * the per-Gaussian constant factors of the 2-D gradients (opacity, -1, -0.5, 0.5*W, 0.5*H) are applied
+        //    once per Gaussian in preprocess_bwd instead of once per (pixel, Gaussian) pair.
+        const float om = __fsub_rn(1.0f, alpha);  // alpha <= 0.99 => om in [0.01, 1]
+        float rinv;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rinv) : "f"(om));
+        rinv = fmaf(rinv, fmaf(-om, rinv, 1.0f), rinv);  // one Newton step: within 1 ulp of 1/om
+        const float Tn = T * rinv;
+        const float cd = fmaf(col.z, dLp2, fmaf(col.y, dLp1, col.x * dLp0));  // <colour, dLp>
+        const float Sn = fmaf(last_alpha, lcd, (1.f - last_alpha) * S);
+        const float dL_dalpha = fmaf(cd - Sn, Tn, -(tfinal_bg * rinv));
+        const float w = valid ? alpha * Tn : 0.f;          // dchannel_dcolor
+        const float q = valid ? G * dL_dalpha : 0.f;       // dL_dopacity; common factor of the 2-D gradients
+        T = valid ? Tn : T;
+        S = valid ? Sn : S;
+        lcd = valid ? cd : lcd;
+        last_alpha = valid ? alpha : last_alpha;
+        const float qx = q * dx, qy = q * dy;
+        const float v0 = w * dLp0, v1 = w * dLp1, v2 = w * dLp2;
+        const float v3 = q;
+        const float v4 = q * fmaf(dy, a.w, dx * a.z);  // * -opacity * 0.5 W  -> dL_dmean2D.x
+        const float v5 = q * fmaf(dx, a.w, dy * b.x);  // * -opacity * 0.5 H  -> dL_dmean2D.y
+        const float v6 = qx * dx;                      // * -0.5 opacity      -> dL_dconic.xx
+        const float v7 = qx * dy;                      //                     -> dL_dconic.xy
+        const float v8 = qy * dy;                      //                     -> dL_dconic.yy
         const float sum = warp_reduce_scatter9(v0, v1, v2, v3, v4, v5, v6, v7, v8, lane);
-        if (commit >= 0) atomicAdd(acc + (size_t)s_id[j] * ACC_STRIDE + commit, sum);
+        const uint32_t off = lds32(chunk_id_addr + bit * 4u) << commit_shift;
+        if (commit >= 0) atomicAdd(commit_base + off, sum);
       }
     }
   }

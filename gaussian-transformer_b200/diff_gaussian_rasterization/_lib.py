@@ -7,7 +7,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(os.path.dirname(_HERE), "lib", "libgsrast.so")
+# GSR_LIB_PATH: development override to A/B another build of the same library
+LIB_PATH = os.environ.get("GSR_LIB_PATH") or os.path.join(os.path.dirname(_HERE), "lib", "libgsrast.so")
 
 
 class gsr_inputs(ctypes.Structure):
