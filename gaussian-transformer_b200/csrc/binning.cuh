@@ -33,6 +33,10 @@ namespace gsr {
 
 constexpr int BIN_WARPS = 4;           // warps per CTA in bin_pass
 constexpr int BAND_TILES_MAX = 2048;   // cursor-table entries per warp (8 KB)
+#ifndef GSR_BAND_ROWS
+#define GSR_BAND_ROWS 1023
+#endif
+constexpr int BAND_ROWS = GSR_BAND_ROWS;  // tile rows per band
 
 struct BinPlan {
   int chunk;       // Gaussians per chunk (multiple of 32)
@@ -49,6 +53,9 @@ inline BinPlan make_bin_plan(int P, int gx, int gy) {
   p.n_chunks = P > 0 ? (P + chunk - 1) / chunk : 0;
   p.rows_per_band = BAND_TILES_MAX / gx;
   if (p.rows_per_band < 1) p.rows_per_band = 0;  // image wider than 32768 px: unsupported, caller reports it
+  // (measured at 1M Gaussians / 1080p: narrower bands -- 2, 4, 8 tile rows -- are slower than the widest band that
+  // fits the cursor table, because every warp scans its whole chunk once per band)
+  if (p.rows_per_band > BAND_ROWS) p.rows_per_band = BAND_ROWS;
   if (p.rows_per_band > gy) p.rows_per_band = gy;
   if (p.rows_per_band > 1023) p.rows_per_band = 1023;  // row offsets travel in 10 bits of a packed shuffle word
   p.n_bands = p.rows_per_band ? (gy + p.rows_per_band - 1) / p.rows_per_band : 0;
@@ -65,6 +72,7 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_pass_kernel(int P, const u
                                                                   const uint2* __restrict__ ranges,
                                                                   uint32_t* __restrict__ point_list) {
   extern __shared__ uint32_t s_tab[];
+  __shared__ uint4 s_desc[BIN_WARPS][32];  // per warp: the step's live Gaussians, compacted in order
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int task = blockIdx.x * BIN_WARPS + w;
   if (task >= plan.n_chunks * plan.n_bands) return;
@@ -73,17 +81,20 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_pass_kernel(int P, const u
   const int ntab = (by1 - by0) * gx;
   const int tile0 = by0 * gx;
   uint32_t* tab = s_tab + w * plan.band_tiles;
+  uint4* desc = s_desc[w];
   uint32_t* row = matrix + (size_t)chunk * gx * gy + tile0;
   for (int t = lane; t < ntab; t += 32) tab[t] = SCATTER ? (__ldg(&ranges[tile0 + t].x) + row[t]) : 0u;
   __syncwarp();
+  const unsigned lt = (1u << lane) - 1u;
   const int begin = chunk * plan.chunk, end = min(P, begin + plan.chunk);
   for (int r0 = begin; r0 < end; r0 += 32) {
     const int k = r0 + lane;
-    uint32_t id = 0, w1 = 0, w2 = 0;  // w1 = x0 | width << 16 ; w2 = (y0 - by0) | height << 10 | magic << 20
+    // descriptor: x = id, y = first table index | width << 16, z = tiles | magic << 16
+    uint4 d = make_uint4(0u, 0u, 0u, 0u);
     bool has = false;
     if (k < end) {
-      id = __ldg(order + k);
-      const float4 a = __ldg(g0 + id);
+      d.x = __ldg(order + k);
+      const float4 a = __ldg(g0 + d.x);
       const int radius = __float_as_int(a.w);
       if (radius > 0) {
         int minx, miny, maxx, maxy;
@@ -92,30 +103,29 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_pass_kernel(int P, const u
         const int y0 = max(miny, by0), y1 = min(maxy, by1);
         has = (y1 > y0) && (maxx > minx);
         if (has) {
-          const int wdt = maxx - minx;
+          const int wdt = maxx - minx, nt = wdt * (y1 - y0);
           // floor(t / wdt) == (t * magic) >> 10 for t < 32, wdt <= 32 (only used when the rect has <= 32 tiles)
           const uint32_t magic = wdt <= 32 ? (1024u + wdt - 1u) / wdt : 0u;
-          w1 = (uint32_t)minx | ((uint32_t)wdt << 16);
-          w2 = (uint32_t)(y0 - by0) | ((uint32_t)(y1 - y0) << 10) | (magic << 20);  // magic <= 1024: 11 bits
+          d.y = (uint32_t)((y0 - by0) * gx + minx) | ((uint32_t)wdt << 16);  // both <= 2048
+          d.z = (uint32_t)nt | (magic << 16);
         }
       }
     }
-    unsigned live = __ballot_sync(0xffffffffu, has);
-    while (live) {
-      const int src = __ffs(live) - 1;
-      live &= live - 1;
-      const uint32_t gid = __shfl_sync(0xffffffffu, id, src);
-      const uint32_t p1 = __shfl_sync(0xffffffffu, w1, src), p2 = __shfl_sync(0xffffffffu, w2, src);
-      const int x0 = p1 & 0xffff, wdt = p1 >> 16, ya = p2 & 0x3ff, hgt = (p2 >> 10) & 0x3ff;
-      const int nt = wdt * hgt;
-      const int rowbase = ya * gx + x0;
+    const unsigned live = __ballot_sync(0xffffffffu, has);
+    if (has) desc[__popc(live & lt)] = d;
+    __syncwarp();
+    const int n_live = __popc(live);
+    // strictly in order, one Gaussian at a time, lanes over the tiles of its rectangle
+    for (int s_ = 0; s_ < n_live; s_++) {
+      const uint4 e = desc[s_];  // broadcast read
+      const int rowbase = e.y & 0xffff, wdt = e.y >> 16, nt = e.z & 0xffff;
       if (nt <= 32) {
         if (lane < nt) {
-          const int ty = (int)(((uint32_t)lane * (p2 >> 20)) >> 10);
+          const int ty = (int)(((uint32_t)lane * (e.z >> 16)) >> 10);
           const int idx = rowbase + ty * gx + (lane - ty * wdt);
           const uint32_t v = tab[idx];
           tab[idx] = v + 1u;
-          if (SCATTER) point_list[v] = gid;
+          if (SCATTER) point_list[v] = e.x;
         }
       } else {
         for (int t = lane; t < nt; t += 32) {
@@ -123,7 +133,7 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_pass_kernel(int P, const u
           const int idx = rowbase + ty * gx + (t - ty * wdt);
           const uint32_t v = tab[idx];
           tab[idx] = v + 1u;
-          if (SCATTER) point_list[v] = gid;
+          if (SCATTER) point_list[v] = e.x;
         }
       }
       __syncwarp();

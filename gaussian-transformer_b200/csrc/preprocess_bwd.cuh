@@ -241,15 +241,17 @@ __device__ __forceinline__ void dir_backward(float dox, float doy, float doz, co
 // coalesced copy of `nfloats` staged floats to global memory (dst 16-byte aligned)
 __device__ __forceinline__ void store_staged(float* __restrict__ dst, const float* s, int nfloats, int tid) {
   const int n4 = nfloats >> 2;
+#pragma unroll 1
   for (int j = tid; j < n4; j += PB_THREADS)
     __stcs(reinterpret_cast<float4*>(dst) + j, reinterpret_cast<const float4*>(s)[j]);
+#pragma unroll 1
   for (int j = (n4 << 2) + tid; j < nfloats; j += PB_THREADS) dst[j] = s[j];
 }
 
 // Staged variant: SH rows of MT coefficients (3*MT floats, a multiple of 4) with 16-byte aligned sh / dL_dsh and
 // 16-byte aligned (P,3)/(P,6) gradient outputs.  MT = 16 (degree <= 3 storage) or 4 (degree <= 1 storage).
 template <int MT>
-__global__ void __launch_bounds__(PB_THREADS) preprocess_bwd_staged_kernel(
+__global__ void __launch_bounds__(PB_THREADS, 5) preprocess_bwd_staged_kernel(
     int P, int D, const float* __restrict__ means3D, const float* __restrict__ scales,
     const float* __restrict__ rotations, const float4* __restrict__ g1, const float* __restrict__ shs,
     const float* __restrict__ cov3D_precomp, Cam cam, const int* __restrict__ radii, const float4* __restrict__ g2,
@@ -280,11 +282,18 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_bwd_staged_kernel(
   __syncthreads();
   if (D > 0) {  // coefficient rows of the visible Gaussians, coalesced (degree 0 needs no coefficient)
     const float4* __restrict__ src4 = reinterpret_cast<const float4*>(shs + (size_t)base * NF);
+    // asynchronous global->shared copies (LDGSTS): no register staging, and the copy overlaps the geometry part
+    // below, which does not need the coefficients
+    const uint32_t tile_addr = (uint32_t)__cvta_generic_to_shared(s_tile);
+#pragma unroll 4
     for (int j = tid; j < nG * F4; j += PB_THREADS) {
       const int row = j / F4, col = j - row * F4;
-      if ((s_vis[row >> 5] >> (row & 31)) & 1u) s_tile[row * RS4 + col] = __ldcs(src4 + j);
+      if ((s_vis[row >> 5] >> (row & 31)) & 1u)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile_addr + (uint32_t)(row * RS4 + col) * 16u),
+                     "l"(src4 + j)
+                     : "memory");
     }
-    __syncthreads();
+    asm volatile("cp.async.commit_group;" ::: "memory");
   }
   GaussGrad o;
 #pragma unroll
@@ -294,9 +303,16 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_bwd_staged_kernel(
 #pragma unroll
   for (int k = 0; k < 4; k++) o.dq[k] = 0.f;
   float4* row4 = s_tile + tid * RS4;
+  float p0 = 0.f, p1 = 0.f, p2 = 0.f;
   if (visible) {
-    const float p0 = __ldg(means3D + 3 * I), p1 = __ldg(means3D + 3 * I + 1), p2 = __ldg(means3D + 3 * I + 2);
+    p0 = __ldg(means3D + 3 * I); p1 = __ldg(means3D + 3 * I + 1); p2 = __ldg(means3D + 3 * I + 2);
     geom_backward(I, scales, rotations, cov3D_precomp, cam, p0, p1, p2, B.x, B.y, B.z, B.w, Cyy, o);
+  }
+  if (D > 0) {
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();
+  }
+  if (visible) {
     const float dox = p0 - __ldg(cam.campos), doy = p1 - __ldg(cam.campos + 1), doz = p2 - __ldg(cam.campos + 2);
     const float len = sqrtf(dox * dox + doy * doy + doz * doz);
     const uint32_t flags = __float_as_uint(__ldg(&g2[i].w));

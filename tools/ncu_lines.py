@@ -14,7 +14,7 @@ import tempfile
 
 rep, pat = sys.argv[1], re.compile(sys.argv[2])
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-so = sys.argv[3] if len(sys.argv) > 3 else os.path.join(ROOT, "gaussian-transformer_b200", "lib", "libgsrast.so")
+so = sys.argv[3] if len(sys.argv) > 3 and sys.argv[3] != "-" else os.path.join(ROOT, "gaussian-transformer_b200", "lib", "libgsrast.so")
 top = int(sys.argv[4]) if len(sys.argv) > 4 else 45
 
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "sass"],
