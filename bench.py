@@ -37,6 +37,9 @@ def parse():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~10-20 s CPU oracle timing")
+    ap.add_argument("--dp-exchange", default="factors", choices=("factors", "allreduce"),
+                    help="N > 1: all-gather 12 B/Gaussian SH factors + all-reduce 44 B/Gaussian (default), or "
+                         "all-reduce the full 236 B/Gaussian")
     return ap.parse_args()
 
 
@@ -192,24 +195,38 @@ def run_ours(args, rank, world, local_rank):
     flat = None
     if world > 1:
         import gsr_dp
-        flat = gsr_dp.FlatGrads({k: tuple(t[k].shape) for k in LEAVES}, dev)
+        keep = LEAVES if args.dp_exchange == "allreduce" else gsr_dp.SMALL_LEAVES
+        flat = gsr_dp.FlatGrads({k: tuple(t[k].shape) for k in keep}, dev)
 
-    def step(src, grads_out=None):
+    def render_backward(src):
         leaves = {k: src[k].detach().requires_grad_(True) for k in LEAVES}
         m2 = torch.zeros_like(leaves["means3D"], requires_grad=True)
         color, radii = raster(means3D=leaves["means3D"], means2D=m2, opacities=leaves["opacities"], shs=leaves["sh"],
                               scales=leaves["scales"], rotations=leaves["rotations"])
         loss = (color * dpix).sum()
         loss.backward()
-        grads = [leaves[k].grad for k in LEAVES]
-        if world > 1:  # per-Gaussian gradients of the replicated parameters: one flat buffer (236 B/Gaussian), one
-            flat.zero_()  # NCCL all-reduce per step (gsr_dp.py)
-            flat.add_({k: leaves[k].grad for k in LEAVES})
-            for w_ in flat.all_reduce(async_op=True):
-                w_.wait()
-            grads = [flat.views[k] for k in LEAVES]
         stats["radii"] = radii
-        return loss, grads
+        return loss, {k: leaves[k].grad for k in LEAVES}
+
+    def step(src):
+        """One step: this rank's view forward + backward, then (N > 1) the gradient exchange of gsr_dp.py."""
+        if world == 1:
+            loss, g = render_backward(src)
+            return loss, [g[k] for k in LEAVES]
+        box = {}
+        if args.dp_exchange == "allreduce":
+            def rb(_v):
+                box["loss"], g = render_backward(src)
+                return g
+            g = gsr_dp.dp_step(rb, world, flat, rank, world)
+        else:
+            def rb(_v):
+                with gsr_dp.capture_sh_factors() as items:
+                    box["loss"], g = render_backward(src)
+                g["sh_factor"] = items[0]
+                return g
+            g = gsr_dp.dp_step_factored(rb, world, flat, rank, world, src["means3D"], SH_DEG, M_COEF)
+        return box["loss"], [g[k] for k in LEAVES]
 
     def sync_all():
         if world > 1:
@@ -297,7 +314,10 @@ def run_ours(args, rank, world, local_rank):
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "gaussians_per_s": value * P_GAUSS,
         "config": {"workload": "C2: scene S (seed 0), 1M Gaussians, SH degree 3, 1920x1080, 1 view per GPU, fwd+bwd"
-                               + ("" if world == 1 else ", NCCL all-reduce of 236 B/Gaussian gradients"),
+                               + ("" if world == 1 else ", NCCL all-reduce of 236 B/Gaussian gradients"
+                                  if args.dp_exchange == "allreduce" else
+                                  ", NCCL all-reduce of 44 B/Gaussian + all-gather of 12 B/Gaussian/view SH factors, "
+                                  "SH gradient rebuilt locally"),
                    "P": P_GAUSS, "visible": V, "num_rendered": R, "W": WIDTH, "H": HEIGHT,
                    "l2": "inputs (236 MB) + scratch exceed the 126 MB L2; no explicit flush"},
         "clocks": clk,

@@ -18,6 +18,7 @@
 #include "preprocess_fwd.cuh"
 #include "render_bwd.cuh"
 #include "render_fwd.cuh"
+#include "sh_exchange.cuh"
 
 using namespace gsr;
 
@@ -336,7 +337,6 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
   if (!dL_dmeans3D || !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dscales || !dL_drotations ||
       !dL_dcov3D || !dL_dconic)
     return fail(GSR_ERR_INVALID, "gsr_backward: NULL gradient output");
-  if (in->sh && in->M > 0 && !dL_dsh) return fail(GSR_ERR_INVALID, "gsr_backward: dL_dsh is NULL");
   const Cam cam = make_cam(in);
   const size_t N = (size_t)in->W * in->H, T = (size_t)cam.gx * cam.gy;
   GeomView g = geom_view(const_cast<void*>(geom), (size_t)in->P);
@@ -363,8 +363,8 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
   out.dL_dconic = dL_dconic;
   ScopedStage prof_(GSR_STAGE_PREPROCESS_BWD, stream);
   // staged (coalesced) variant: SH rows of 16 or 4 coefficients and 16-byte aligned arrays; else the generic one
-  const bool staged = in->sh && out.dL_dsh && (in->M == 16 || in->M == 4) && aligned16(in->sh) &&
-                      aligned16(dL_dsh) && aligned16(dL_dmeans3D) && aligned16(dL_dmeans2D) &&
+  const bool staged = in->sh && (in->M == 16 || in->M == 4) && aligned16(in->sh) &&
+                      (!out.dL_dsh || aligned16(dL_dsh)) && aligned16(dL_dmeans3D) && aligned16(dL_dmeans2D) &&
                       aligned16(dL_dcolors) && aligned16(dL_dscales) && aligned16(dL_dcov3D) &&
                       aligned16(dL_dconic) && aligned16(dL_drotations);
   const int pb_blocks = (in->P + PB_THREADS - 1) / PB_THREADS;
@@ -384,6 +384,36 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
                                                                 cam, radii, g.g2, bw, out);
   }
   GSR_STAGE("preprocess_bwd", in->debug, stream);
+  return GSR_OK;
+}
+
+int gsr_sh_color_factors(int32_t P, const void* geom, const float* dL_dcolors, float* factors, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0) return fail(GSR_ERR_INVALID, "gsr_sh_color_factors: P < 0");
+  if (P == 0) return GSR_OK;
+  if (!geom || !dL_dcolors || !factors) return fail(GSR_ERR_INVALID, "gsr_sh_color_factors: NULL pointer");
+  GeomView g = geom_view(const_cast<void*>(geom), (size_t)P);
+  sh_color_factors_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.g2, dL_dcolors, factors);
+  GSR_STAGE("sh_color_factors", 0, stream);
+  return GSR_OK;
+}
+
+int gsr_sh_grad_from_factors(int32_t P, int32_t D, int32_t M, int32_t V, const float* means3D, const float* campos,
+                             const float* factors, float* dL_dsh, int32_t accumulate, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0 || V < 0 || M <= 0 || D < 0 || D > 3 || (D + 1) * (D + 1) > M)
+    return fail(GSR_ERR_INVALID, "gsr_sh_grad_from_factors: bad P / V / D / M");
+  if (P == 0) return GSR_OK;
+  if (!means3D || !dL_dsh || (V > 0 && (!campos || !factors)))
+    return fail(GSR_ERR_INVALID, "gsr_sh_grad_from_factors: NULL pointer");
+  const int blocks = (P + PB_THREADS - 1) / PB_THREADS;
+  if (M == 16 && aligned16(dL_dsh))
+    sh_grad_from_factors_kernel<true><<<blocks, PB_THREADS, PB_THREADS * 13 * 16, stream>>>(
+        P, D, M, V, means3D, campos, factors, dL_dsh, accumulate);
+  else
+    sh_grad_from_factors_kernel<false><<<blocks, PB_THREADS, 0, stream>>>(P, D, M, V, means3D, campos, factors,
+                                                                         dL_dsh, accumulate);
+  GSR_STAGE("sh_grad_from_factors", 0, stream);
   return GSR_OK;
 }
 

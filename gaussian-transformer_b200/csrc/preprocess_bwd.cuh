@@ -352,7 +352,7 @@ __global__ void __launch_bounds__(PB_THREADS, 5) preprocess_bwd_staged_kernel(
     __stcs(reinterpret_cast<float4*>(out.dL_drot) + I, make_float4(o.dq[0], o.dq[1], o.dq[2], o.dq[3]));
   }
   __syncthreads();
-  {  // dL_dsh rows: nG * F4 contiguous float4
+  if (out.dL_dsh != nullptr) {  // dL_dsh rows: nG * F4 contiguous float4 (NULL: the caller exchanges SH factors)
     float4* __restrict__ dst4 = reinterpret_cast<float4*>(out.dL_dsh + (size_t)base * NF);
     for (int j = tid; j < nG * F4; j += PB_THREADS) {
       const int row = j / F4, col = j - row * F4;

@@ -103,15 +103,19 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh,
-                                 degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug):
-    """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations)."""
+                                 degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, sh_grad=True):
+    """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
+
+    sh_grad=False (extension, used by gsr_dp): dL_dsh is not computed and returned as None; the caller rebuilds it
+    from sh_color_factors()/sh_grad_from_factors()."""
     _check_means(means3D)
     dev = means3D.device
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
     f32 = dict(dtype=torch.float32, device=dev)
-    g = dict(means3D=torch.empty(P, 3, **f32), means2D=torch.empty(P, 3, **f32), sh=torch.empty(P, M, 3, **f32),
+    g = dict(means3D=torch.empty(P, 3, **f32), means2D=torch.empty(P, 3, **f32),
+             sh=torch.empty(P, M, 3, **f32) if sh_grad else None,
              colors=torch.empty(P, 3, **f32), opacity=torch.empty(P, 1, **f32), scales=torch.empty(P, 3, **f32),
              rot=torch.empty(P, 4, **f32), cov3D=torch.empty(P, 6, **f32), conic=torch.empty(P, 2, 2, **f32))
     if P != 0:
@@ -128,12 +132,46 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             _lib.check(_lib.lib.gsr_backward(
                 ctypes.byref(args), radii.data_ptr(), geomBuffer.data_ptr(),
                 binningBuffer.data_ptr() if binningBuffer.numel() else 0, imageBuffer.data_ptr(), int(R),
-                dpix.data_ptr(), g["means3D"].data_ptr(), g["means2D"].data_ptr(), _ptr(g["sh"]) if M else 0,
+                dpix.data_ptr(), g["means3D"].data_ptr(), g["means2D"].data_ptr(), _ptr(g["sh"]) if (M and sh_grad) else 0,
                 g["colors"].data_ptr(), g["opacity"].data_ptr(), g["scales"].data_ptr(), g["rot"].data_ptr(),
                 g["cov3D"].data_ptr(), g["conic"].data_ptr(), work.data_ptr(),
                 torch.cuda.current_stream(dev).cuda_stream))
     rasterize_gaussians_backward.last_dL_dconic = g["conic"]  # exposed for the parity tests only
     return (g["means2D"], g["colors"], g["opacity"], g["means3D"], g["cov3D"], g["sh"], g["scales"], g["rot"])
+
+
+def sh_color_factors(geomBuffer, dL_dcolors):
+    """(P,3) dL/dcolor of one view with the channels the forward clamped zeroed: the per-Gaussian factor of that
+    view's rank-1 SH gradient (include/gsrast.h gsr_sh_color_factors)."""
+    P = dL_dcolors.size(0)
+    dev = dL_dcolors.device
+    out = torch.empty(P, 3, dtype=torch.float32, device=dev)
+    if P != 0:
+        with torch.cuda.device(dev):
+            c = _f32(dL_dcolors, dev)
+            _lib.check(_lib.lib.gsr_sh_color_factors(P, geomBuffer.data_ptr(), c.data_ptr(), out.data_ptr(),
+                                                     torch.cuda.current_stream(dev).cuda_stream))
+    return out
+
+
+def sh_grad_from_factors(means3D, campos, factors, degree, M, out=None):
+    """(P,M,3) sum over views v of basis(normalize(means3D - campos[v])) (x) factors[v]; campos (V,3), factors
+    (V,P,3).  out: accumulate into an existing (P,M,3) tensor instead of allocating."""
+    _check_means(means3D)
+    dev = means3D.device
+    P, V = means3D.size(0), campos.size(0)
+    if factors.shape != (V, P, 3):
+        raise RuntimeError("factors must have dimensions (num_views, num_points, 3)")
+    acc = out is not None
+    if not acc:
+        out = torch.empty(P, M, 3, dtype=torch.float32, device=dev)
+    if P != 0:
+        with torch.cuda.device(dev):
+            m, c, f = _f32(means3D, dev), _f32(campos, dev), _f32(factors, dev)
+            _lib.check(_lib.lib.gsr_sh_grad_from_factors(P, int(degree), int(M), V, m.data_ptr(), _ptr(c), _ptr(f),
+                                                         out.data_ptr(), int(acc),
+                                                         torch.cuda.current_stream(dev).cuda_stream))
+    return out
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

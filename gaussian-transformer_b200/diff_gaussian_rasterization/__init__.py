@@ -37,6 +37,13 @@ class GaussianRasterizationSettings(NamedTuple):
     debug: bool
 
 
+# Extension used by gsr_dp (data-parallel over views): while a sink list is installed, the backward of a call
+# that used SHs does not compute dL/dsh (the gradient returned for `shs` is None); it appends
+# (campos, factors (P,3)) of the view to the sink instead, and gsr_dp rebuilds the summed SH gradient after
+# exchanging the factors between ranks.  None (the default) = reference behaviour.
+_sh_factor_sink = None
+
+
 def _snapshot(args, path, note):
     """debug=True contract (DGR __init__.py:83-90,132-139): dump the argument tuple on failure."""
     cpu = tuple(a.detach().cpu().clone() if isinstance(a, torch.Tensor) else a for a in args)
@@ -80,13 +87,16 @@ class _RasterizeGaussians(torch.autograd.Function):
         dump = _snapshot(call, "snapshot_bw.dump",
                          "\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n") \
             if s.debug else None
+        sink = _sh_factor_sink if (sh is not None and sh.numel() != 0) else None
         try:
             (g_means2D, g_colors, g_opac, g_means3D, g_cov3D, g_sh, g_scales,
-             g_rot) = _C.rasterize_gaussians_backward(*call)
+             g_rot) = _C.rasterize_gaussians_backward(*call, sh_grad=sink is None)
         except Exception:
             if dump:
                 dump()
             raise
+        if sink is not None:
+            sink.append((s.campos.detach().reshape(3), _C.sh_color_factors(geom, g_colors)))
         # order of forward's inputs; the settings tuple gets None (DGR __init__.py:143-153)
         return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None
 

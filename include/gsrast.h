@@ -125,7 +125,7 @@ GSR_API int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binni
  * so the caller may pass uninitialised memory.
  *   dL_dpix      float[3*H*W]  upstream gradient of out_color
  *   dL_dmeans3D  float[P*3]    dL_dmeans2D float[P*3] (z = 0)
- *   dL_dsh       float[P*M*3]  (NULL allowed when sh is absent)
+ *   dL_dsh       float[P*M*3]  (NULL allowed: sh absent, or the caller rebuilds it from exchanged factors, below)
  *   dL_dcolors   float[P*3]    dL_dopacity float[P]
  *   dL_dscales   float[P*3]    dL_drotations float[P*4]
  *   dL_dcov3D    float[P*6]    dL_dconic float[P*4] ((P,2,2): xx, xy, -, yy)
@@ -136,6 +136,22 @@ GSR_API int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void*
                  float* dL_dsh, float* dL_dcolors, float* dL_dopacity,
                  float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
                  float* dL_dconic, void* bwd_scratch, void* stream);
+
+/* Data-parallel SH gradient exchange (no reference counterpart: the reference is single-GPU; this serves the
+ * view-sharded path of SURVEY.md section 8e).  For one view, dL/dsh(i,k,c) = basis_k(dir_i) * f(i,c) with
+ * f = dL/dcolor whose forward-clamped channels are zeroed (DGR/cuda_rasterizer/backward.cu:20-139), a rank-1
+ * product per Gaussian.  Ranks all-gather f (12 B per Gaussian per view) instead of all-reducing 12*M B per
+ * Gaussian, call gsr_backward with dL_dsh = NULL, and rebuild the sum over all views locally:
+ *   gsr_sh_color_factors:      factors float[P*3] out, from the dL_dcolors of gsr_backward and the geom buffer of
+ *                              the same forward;
+ *   gsr_sh_grad_from_factors:  dL_dsh float[P*M*3] (+)= sum_v basis(normalize(means3D - campos[v])) (x) factors[v];
+ *                              campos float[V*3] and factors float[V*P*3] are DEVICE arrays; accumulate = 0
+ *                              overwrites (every element written), 1 adds to the existing content. */
+GSR_API int gsr_sh_color_factors(int32_t P, const void* geom, const float* dL_dcolors, float* factors,
+                                 void* stream);
+GSR_API int gsr_sh_grad_from_factors(int32_t P, int32_t D, int32_t M, int32_t V, const float* means3D,
+                                     const float* campos, const float* factors, float* dL_dsh,
+                                     int32_t accumulate, void* stream);
 
 /* present[i] = (view-space z > 0.2).  Replaces Rasterizer::markVisible /
  * checkFrustum (DGR/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153). */

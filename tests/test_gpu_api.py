@@ -38,6 +38,48 @@ def test_autograd_matches_reference(reference):
     assert float(m2.grad[:, 2].abs().max()) == 0.0
 
 
+def test_sh_factor_exchange_matches_plain_sh_gradient():
+    """gsr_dp's SH path: backward without dL/dsh + (campos, factors) per view + local rebuild over two views must
+    equal the sum of the two views' ordinary SH gradients; the other gradients are unchanged."""
+    import gsr_dp
+    grads, items_all, means = [], [], None
+    for yaw in (-10.0, 12.0):
+        sc = S.scene_S(3000, 320, 208, seed=5, M=16, sh_degree=3, yaw_deg=yaw)
+        d = to_device(sc)
+        dpix = torch.from_numpy(S.upstream_grad(sc["W"], sc["H"], 5)).cuda()
+        out = []
+        for capture in (False, True):
+            m3, sh, op, scl, rot = (_leaf(d[k]) for k in ("means3D", "sh", "opacities", "scales", "rotations"))
+            items = []
+            if capture:
+                with gsr_dp.capture_sh_factors() as items:
+                    color, _ = _module(d)(means3D=m3, means2D=torch.zeros_like(m3), opacities=op, shs=sh, scales=scl,
+                                          rotations=rot)
+                    (color * dpix).sum().backward()
+                assert sh.grad is None and len(items) == 1
+                items_all.append(items[0])
+            else:
+                color, _ = _module(d)(means3D=m3, means2D=torch.zeros_like(m3), opacities=op, shs=sh, scales=scl,
+                                      rotations=rot)
+                (color * dpix).sum().backward()
+            out.append((m3.grad, op.grad, scl.grad, rot.grad, sh.grad))
+        for a, b in zip(out[0][:4], out[1][:4]):
+            assert rel_err(np_(b), np_(a)) <= 1e-3  # atomics order only
+        grads.append(out[0][4])
+        means = d["means3D"]
+    cam, fac = gsr_dp.gather_sh_factors(items_all, 2, 3000, means.device, 1)
+    from diff_gaussian_rasterization import _C
+    rebuilt = _C.sh_grad_from_factors(means, cam, fac, 3, 16)
+    want = grads[0] + grads[1]
+    assert float(want.abs().max()) > 0
+    assert rel_err(np_(rebuilt), np_(want)) <= 1e-3
+    again = _C.sh_grad_from_factors(means, cam, fac, 3, 16, out=rebuilt.clone())  # accumulate mode
+    assert rel_err(np_(again), np_(2 * rebuilt)) <= 1e-6
+    # generic (non-staged) variant: M = 4, degree 1
+    r4 = _C.sh_grad_from_factors(means, cam, fac, 1, 4)
+    assert rel_err(np_(r4), np_(_C.sh_grad_from_factors(means, cam, fac, 1, 16)[:, :4])) <= 1e-6
+
+
 def test_colors_and_cov_paths():
     sc, _ = cases.case("s_deg3")
     d = to_device(sc)
