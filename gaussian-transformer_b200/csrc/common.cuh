@@ -77,7 +77,10 @@ struct BwdView {
 // ctrl[] slots
 enum { CTRL_FLAGS = 0, CTRL_R_LO = 4, CTRL_R_HI = 5, CTRL_WORDS = 64 };
 
-constexpr int SORT_TILE_KEYS = 4096;  // keys per CTA in depth_sort.cuh (RS_TILE)
+#ifndef GSR_SORT_ROUNDS
+#define GSR_SORT_ROUNDS 4
+#endif
+constexpr int SORT_TILE_KEYS = 256 * GSR_SORT_ROUNDS;  // keys per CTA in depth_sort.cuh (RS_TILE)
 inline size_t sort_ctas(size_t P) { return (P + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS; }
 inline size_t bin_chunks(size_t P) {  // must match make_bin_plan (binning.cuh)
   size_t chunk = (P + 1023) / 1024;

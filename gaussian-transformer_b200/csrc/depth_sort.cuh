@@ -21,8 +21,9 @@ namespace gsr {
 
 constexpr int RS_THREADS = 256;
 constexpr int RS_WARPS = RS_THREADS / 32;
-constexpr int RS_ROUNDS = 16;                         // keys per thread
-constexpr int RS_TILE = RS_THREADS * RS_ROUNDS;       // 4096 keys per CTA
+constexpr int RS_ROUNDS = GSR_SORT_ROUNDS;             // keys per thread
+constexpr int RS_TILE = RS_THREADS * RS_ROUNDS;       // keys per CTA
+static_assert(RS_TILE == SORT_TILE_KEYS, "scratch sizing and the sort disagree");
 constexpr int RS_SEG = 32 * RS_ROUNDS;                // 512 keys per warp
 
 __global__ void __launch_bounds__(RS_THREADS) radix_hist_kernel(const uint32_t* __restrict__ keys, int n, int shift,

@@ -92,3 +92,27 @@ def covariance_from_scale_rot(scales, rotations, mod=1.0):
     L = R * (mod * scales.astype(np.float64))[:, None, :]
     S = L @ L.transpose(0, 2, 1)
     return np.stack([S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]], 1).astype(np.float32)
+
+
+def scene_C1(points_npz, W=800, H=450, M=16, sh_degree=3):
+    """BASELINE config 1: the bundled tiramisu_ds COLMAP points as Gaussians, initialised exactly like
+    GaussianModel.create_from_pcd (scene/gaussian_model.py:124-147): DC = RGB2SH(colour) (utils/sh_utils.py:114-115),
+    rest 0, scale = sqrt(mean 3-NN distance^2) on all axes (clamped at 1e-7 before the root), rotation (1,0,0,0),
+    opacity 0.1.  Camera: COLMAP world frame, identity pose (the cloud sits in front of it), focal 3287.46 px at
+    4032 px width (cameras.bin) rescaled to W (utils/camera_utils.py:35-39).  `points_npz`: the fixture written by
+    tests/golden/make_c1_points.py."""
+    z = np.load(points_npz)
+    xyz, rgb, dist2 = z["xyz"].astype(np.float32), z["rgb"], z["dist2"].astype(np.float32)
+    P = xyz.shape[0]
+    fovx = 2.0 * math.atan(4032.0 / (2.0 * 3287.46))
+    cam = look_at_camera(W, H, math.degrees(fovx), 0.0)
+    sh = np.zeros((P, M, 3), dtype=np.float32)
+    sh[:, 0, :] = ((rgb.astype(np.float32) / 255.0) - 0.5) / SH_C0
+    s = np.sqrt(np.maximum(dist2, 1e-7)).astype(np.float32)
+    rot = np.zeros((P, 4), dtype=np.float32)
+    rot[:, 0] = 1.0
+    out = dict(cam)
+    out.update(P=P, M=M, sh_degree=sh_degree, means3D=xyz, scales=np.repeat(s[:, None], 3, 1).copy(), rotations=rot,
+               opacities=np.full((P, 1), 0.1, dtype=np.float32), sh=sh, bg=np.zeros(3, dtype=np.float32),
+               scale_modifier=1.0)
+    return out

@@ -1,6 +1,7 @@
 """Named parity cases: small seeded scenes covering the reference's argument combinations and edge cases
 (SURVEY.md A.8).  Each returns (scene dict of numpy arrays, options)."""
 import math
+import os
 
 import numpy as np
 
@@ -33,6 +34,9 @@ def case(name):
     elif name == "s_cov3d":
         sc = _base(seed=9)
         opt["cov3D_precomp"] = True
+    elif name == "c1_tiramisu":  # BASELINE config 1: bundled COLMAP points as Gaussians, 800x450
+        sc = S.scene_C1(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "data",
+                                     "c1_tiramisu_points.npz"))
     elif name == "s_big":  # large splats: long per-tile lists, early termination, big-sort path
         sc = _base(P=12000, W=160, H=96, seed=10, log_scale_mean=math.log(0.15))
     elif name == "s_huge_lists":  # lists longer than the shared-memory sort capacity (global fallback)
@@ -71,7 +75,7 @@ def case(name):
 
 
 ALL = ["s_deg3", "s_deg0", "s_deg1_m4", "s_deg2_m9", "s_deg0_m1", "s_deg2_m16", "s_bg_yaw", "s_colors", "s_cov3d",
-       "s_big", "s_huge_lists", "s_dense_opaque", "s_scale_mod", "s_exact_tiles", "all_culled", "one_huge", "nonfinite"]
+       "c1_tiramisu", "s_big", "s_huge_lists", "s_dense_opaque", "s_scale_mod", "s_exact_tiles", "all_culled", "one_huge", "nonfinite"]
 GOLDEN = ["s_deg3", "s_deg1_m4", "s_bg_yaw", "s_colors", "s_cov3d", "one_huge"]
 
 

@@ -63,7 +63,21 @@ def _check_image(ours, ref, exact_ncontrib=True):
         assert (diff > IMG_TOL).mean() <= 2e-4 and diff.max() < 2e-2, (diff.max(), (diff > IMG_TOL).mean())
 
 
-def _check_grads(ours, ref, tol=GRAD_TOL, ref_again=None, arbiter=None):
+def _rot_floor(ref, sc):
+    """Natural scale of dL/drot: it is a sum of products of dL/dcov3D with squared scales that cancels EXACTLY for
+    an isotropic Gaussian (BASELINE config 1 initialises every Gaussian isotropic with identity rotation: the true
+    gradient is 0 and both implementations return rounding noise, reference 4e-13, ours 1e-12).  Errors of
+    dL/drot are therefore measured against max(|ref|, max_i scale_i^2 * |dL/dcov3D_i|)."""
+    if sc is None or "cov3D" not in ref or np_(ref["cov3D"]).size == 0:
+        return 0.0
+    s = np.abs(np.asarray(sc["scales"], dtype=np.float64)).max(1) * float(sc["scale_modifier"])
+    c = np.abs(np.nan_to_num(np_(ref["cov3D"]).astype(np.float64), nan=0.0, posinf=0.0, neginf=0.0)).max(1)
+    with np.errstate(over="ignore", invalid="ignore"):
+        v = np.nan_to_num(s * s * c, nan=0.0, posinf=0.0)
+    return float(v.max()) if v.size else 0.0
+
+
+def _check_grads(ours, ref, tol=GRAD_TOL, ref_again=None, arbiter=None, sc=None):
     """ref_again: a second run of the reference on the same inputs.  Its fp32 atomics are order-nondeterministic, so
     on ill-conditioned Gaussians it differs from ITSELF by more than 1e-3 at 1M Gaussians (measured: rot 1.3e-3 ..
     4.4e-3, cov3D 2e-4 .. 6e-4 over six runs); the bar for a tensor is then max(1e-3, 3 x the reference's own
@@ -81,6 +95,11 @@ def _check_grads(ours, ref, tol=GRAD_TOL, ref_again=None, arbiter=None):
         fin = np.isfinite(b.reshape(a.shape))
         assert (np.isfinite(a) == fin).all(), k
         e = rel_err(np.where(fin, a, 0), np.where(fin, b.reshape(a.shape), 0))
+        if k == "rot":
+            bm = float(np.abs(np.where(fin, b.reshape(a.shape), 0)).max())
+            floor = _rot_floor(ref, sc)
+            if floor > bm:
+                e = e * (bm / floor) if bm > 0 else float(np.abs(np.where(fin, a, 0)).max()) / floor
         tol_k = tol
         if ref_again is not None:
             tol_k = max(tol, 3.0 * rel_err(np.where(fin, np_(ref_again[k]).reshape(a.shape), 0),
@@ -104,7 +123,7 @@ def test_vs_reference_cuda(name, reference):
     dpix = torch.from_numpy(S.upstream_grad(sc["W"], sc["H"], seed=99)).cuda()
     g_ref = reference.backward(dpix)
     g = ours_backward(d, ours, dpix, colors_precomp=cp, cov3D_precomp=cv)
-    _check_grads(g, g_ref)
+    _check_grads(g, g_ref, sc=sc if cov is None else None)
 
 
 @pytest.mark.parametrize("name", [n for n in cases.ALL if n != "nonfinite"])
@@ -117,7 +136,7 @@ def test_vs_cpu_oracle(name, oracle):
     dpix = S.upstream_grad(sc["W"], sc["H"], seed=99)
     g_orc = oracle.backward(dpix)
     g = ours_backward(d, ours, torch.from_numpy(dpix).cuda(), colors_precomp=cp, cov3D_precomp=cv)
-    _check_grads(g, g_orc, tol=5e-3)  # the oracle may differ on the isolated threshold pixels above
+    _check_grads(g, g_orc, tol=5e-3, sc=sc if cov is None else None)  # the oracle may differ on the isolated threshold pixels above
 
 
 def test_nan_covariance_is_culled_not_rendered(oracle):
@@ -139,6 +158,20 @@ def test_debug_mode_and_determinism():
     b = ours_forward(d)
     for k in ("radii", "point_list", "ranges", "n_contrib", "color"):
         assert torch.equal(a[k], b[k]), k
+
+
+def test_4k_forward_vs_reference(reference):
+    """BASELINE config 5 shape (3840x2160, 32,400 tiles, 47-bit reference sort keys), forward only, at 2M Gaussians
+    to keep the test short: lists, ranges, n_contrib bit-exact, image within 1e-5."""
+    sc = S.scene_S(2_000_000, 3840, 2160, seed=3)
+    d = to_device(sc)
+    ref = reference.forward(d)
+    ours = ours_forward(d)
+    _check_forward(ours, ref, has_rgb=True)
+    _check_image(ours, ref)
+    r = np_(ours["ranges"]).astype(np.int64)
+    ne = r[:, 1] > r[:, 0]
+    assert (r[ne, 0][1:] == r[ne, 1][:-1]).all() and r[ne, 1][-1] == ours["num_rendered"]
 
 
 @pytest.mark.parametrize("P,W,H", [(200_000, 1920, 1080), (1_000_000, 1920, 1080)])
