@@ -192,6 +192,18 @@ __device__ __forceinline__ float gauss_power(float dx, float dy, float A, float 
   return __fmaf_rn(s, -0.5f, -v);
 }
 
+// Same value, same roundings, with Blackwell's packed fp32 pipe (FADD2 / FMUL2: two IEEE fp32 operations per
+// issued instruction; the blend kernels are issue-bound).  m = (mean.x, mean.y), npix = (-pix.x, -pix.y),
+// AC = (conic A, conic C).  d = (dx, dy) and p = (dx*A, dy*C) are returned for reuse by the backward.
+__device__ __forceinline__ float gauss_power2(float2 m, float2 npix, float2 AC, float B, float2& d, float2& p) {
+  d = __fadd2_rn(m, npix);
+  p = __fmul2_rn(d, AC);
+  const float t1 = __fmul_rn(d.y, p.y);
+  const float s = __fmaf_rn(d.x, p.x, t1);
+  const float v = __fmul_rn(d.y, __fmul_rn(d.x, B));
+  return __fmaf_rn(s, -0.5f, -v);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
   v += __shfl_xor_sync(0xffffffffu, v, 16);
   v += __shfl_xor_sync(0xffffffffu, v, 8);

@@ -20,26 +20,30 @@
 
 namespace gsr {
 
-// pair step of the reduce-scatter: lanes with `hi` clear end up with sum(a), lanes with it set with sum(b)
-__device__ __forceinline__ float rs_pair(float a, float b, bool hi, int xorm) {
-  const float send = hi ? a : b;
-  const float keep = hi ? b : a;
-  return keep + __shfl_xor_sync(0xffffffffu, send, xorm);
+// Reduce-scatter butterfly over the warp for 9 values.  One level: lanes whose bit `xorm` is clear keep the first
+// value of each pair and receive the partner's copy of it, the others the second; the adds of two pairs are issued
+// as one packed FADD2.  After the call, lane l with (l & 3) == 0 holds the warp-wide sum of
+// v[4*b2 + 2*b3 + b4] (b2 = bit 2 of l, ...), and lanes with (l & 2) hold the sum of v8.
+__device__ __forceinline__ float2 rs_pair2(float a0, float b0, float a1, float b1, bool hi, int xorm) {
+  const float2 send = make_float2(hi ? a0 : b0, hi ? a1 : b1);
+  const float2 keep = make_float2(hi ? b0 : a0, hi ? b1 : a1);
+  return __fadd2_rn(keep, make_float2(__shfl_xor_sync(0xffffffffu, send.x, xorm),
+                                      __shfl_xor_sync(0xffffffffu, send.y, xorm)));
 }
 
-// After the call, lane l with (l & 3) == 0 holds the warp-wide sum of v[4*b2 + 2*b3 + b4]
-// (b2 = bit 2 of l, ...), and lanes with (l & 2) hold the sum of v8.
 __device__ __forceinline__ float warp_reduce_scatter9(float v0, float v1, float v2, float v3, float v4, float v5,
                                                       float v6, float v7, float v8, int lane) {
   const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2;
-  const float r0 = rs_pair(v0, v1, b4, 16), r1 = rs_pair(v2, v3, b4, 16), r2 = rs_pair(v4, v5, b4, 16),
-              r3 = rs_pair(v6, v7, b4, 16);
+  const float2 r01 = rs_pair2(v0, v1, v2, v3, b4, 16), r23 = rs_pair2(v4, v5, v6, v7, b4, 16);
   float s = v8 + __shfl_xor_sync(0xffffffffu, v8, 16);
-  const float t0 = rs_pair(r0, r1, b3, 8), t1 = rs_pair(r2, r3, b3, 8);
+  const float2 t01 = rs_pair2(r01.x, r01.y, r23.x, r23.y, b3, 8);
   s += __shfl_xor_sync(0xffffffffu, s, 8);
-  const float u0 = rs_pair(t0, t1, b2, 4);
-  s += __shfl_xor_sync(0xffffffffu, s, 4);
-  float w = rs_pair(u0, s, b1, 2);
+  // level xor 4: the pair (t01.x, t01.y) and the running s advance together
+  const float send = b2 ? t01.x : t01.y, keep = b2 ? t01.y : t01.x;
+  const float2 us = __fadd2_rn(make_float2(keep, s), make_float2(__shfl_xor_sync(0xffffffffu, send, 4),
+                                                                 __shfl_xor_sync(0xffffffffu, s, 4)));
+  const float send2 = b1 ? us.x : us.y, keep2 = b1 ? us.y : us.x;
+  float w = keep2 + __shfl_xor_sync(0xffffffffu, send2, 2);
   w += __shfl_xor_sync(0xffffffffu, w, 1);
   return w;
 }
@@ -63,7 +67,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
   warp_pixel(tid, lx, ly);
   const int pix_x = blockIdx.x * TILE + lx, pix_y = blockIdx.y * TILE + ly;
   const bool inside = pix_x < W && pix_y < H;
-  const float pfx = (float)pix_x, pfy = (float)pix_y;
+  const float2 npix = make_float2(-(float)pix_x, -(float)pix_y);
   const float tx0 = (float)(blockIdx.x * TILE), ty0 = (float)(blockIdx.y * TILE);
   const float wx0 = tx0 + (float)(((tid >> 5) & 1) << 3), wy0 = ty0 + (float)(((tid >> 5) >> 1) << 2);
   const uint2 range = ranges[blockIdx.y * gridDim.x + blockIdx.x];
@@ -115,7 +119,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
         const float4 a = s_rec[c0 + lane].a, b = s_rec[c0 + lane].b;
         CullPre pre;
         pre.thr = b.z; pre.rBC = b.w; pre.rBA = s_rba[c0 + lane];
-        hit = !cull_rect(a.x, a.y, a.z, a.w, b.x, pre, wx0, wx0 + 7.f, wy0, wy0 + 3.f);
+        hit = !cull_rect(a.x, a.y, a.z, b.x, a.w, pre, wx0, wx0 + 7.f, wy0, wy0 + 3.f);
       }
       unsigned mask = __ballot_sync(0xffffffffu, hit);
       const uint32_t chunk_addr = rec_addr + (uint32_t)c0 * (uint32_t)sizeof(StageRec);
@@ -127,8 +131,8 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
         const float4 a = lds128(addr);
         const float2 b = lds64(addr + 16);
         const float4 col = lds128(addr + 32);
-        const float dx = __fsub_rn(a.x, pfx), dy = __fsub_rn(a.y, pfy);
-        const float power = gauss_power(dx, dy, a.z, a.w, b.x);
+        float2 d, pp;  // (dx, dy), (dx*A, dy*C)
+        const float power = gauss_power2(make_float2(a.x, a.y), npix, make_float2(a.z, a.w), b.x, d, pp);
         const float G = expf(power);
         const float alpha = fminf(0.99f, __fmul_rn(b.y, G));
         // same acceptance as the forward (backward.cu:488-497): behind the last contributor, power > 0 and
@@ -154,15 +158,15 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
         S = valid ? Sn : S;
         lcd = valid ? cd : lcd;
         last_alpha = valid ? alpha : last_alpha;
-        const float qx = q * dx, qy = q * dy;
-        const float v0 = w * dLp0, v1 = w * dLp1, v2 = w * dLp2;
-        const float v3 = q;
-        const float v4 = q * fmaf(dy, a.w, dx * a.z);  // * -opacity * 0.5 W  -> dL_dmean2D.x
-        const float v5 = q * fmaf(dx, a.w, dy * b.x);  // * -opacity * 0.5 H  -> dL_dmean2D.y
-        const float v6 = qx * dx;                      // * -0.5 opacity      -> dL_dconic.xx
-        const float v7 = qx * dy;                      //                     -> dL_dconic.xy
-        const float v8 = qy * dy;                      //                     -> dL_dconic.yy
-        const float sum = warp_reduce_scatter9(v0, v1, v2, v3, v4, v5, v6, v7, v8, lane);
+        const float2 qq = make_float2(q, q);
+        const float2 v01 = __fmul2_rn(make_float2(w, w), make_float2(dLp0, dLp1));
+        const float v2 = w * dLp2;
+        // (dx*A + dy*B, dy*C + dx*B) * q   -> dL_dmean2D.xy (* -opacity * 0.5 W / 0.5 H in preprocess_bwd)
+        const float2 v45 = __fmul2_rn(qq, make_float2(fmaf(d.y, b.x, pp.x), fmaf(d.x, b.x, pp.y)));
+        const float2 qd = __fmul2_rn(qq, d);
+        const float2 v68 = __fmul2_rn(qd, d);  // q dx dx, q dy dy  -> dL_dconic.xx, .yy (* -0.5 opacity)
+        const float v7 = qd.x * d.y;           //                   -> dL_dconic.xy
+        const float sum = warp_reduce_scatter9(v01.x, v01.y, v2, q, v45.x, v45.y, v68.x, v7, v68.y, lane);
         const uint32_t off = lds32(chunk_id_addr + bit * 4u) << commit_shift;
         if (commit >= 0) atomicAdd(commit_base + off, sum);
       }
