@@ -40,6 +40,7 @@ __host__ __device__ inline size_t align_up(size_t v) { return (v + ALIGN - 1) & 
 //   g2 float4[P]  r, g, b, flags (bits 0..2 = clamped r/g/b, bits 3.. = tiles_touched)
 //   keys[2] u32[P], vals[2] u32[P]  depth-sort ping-pong (keys = depth bits, 0xffffffff for culled)
 //   cta_hist u32[256 * n_sort_cta + 256]  radix digit histograms (digit-major) + digit totals
+//   rects uint2[P]  clipped tile rectangle of the k-th Gaussian in depth order (binning.cuh)
 // image
 //   final_T f32[N], n_contrib u32[N], ranges uint2[T], tile_count u32[T], ctrl u32[64],
 //   matrix u32[n_chunks * T] (binning.cuh)
@@ -56,6 +57,7 @@ struct GeomView {
   uint32_t* keys[2];
   uint32_t* vals[2];
   uint32_t* cta_hist;
+  uint2* rects;
 };
 struct ImageView {
   float* final_T;
@@ -82,15 +84,14 @@ enum { CTRL_FLAGS = 0, CTRL_R_LO = 4, CTRL_R_HI = 5, CTRL_WORDS = 64 };
 #endif
 constexpr int SORT_TILE_KEYS = 256 * GSR_SORT_ROUNDS;  // keys per CTA in depth_sort.cuh (RS_TILE)
 inline size_t sort_ctas(size_t P) { return (P + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS; }
-inline size_t bin_chunks(size_t P) {  // must match make_bin_plan (binning.cuh)
-  size_t chunk = (P + 1023) / 1024;
-  if (chunk < 1024) chunk = 1024;
-  chunk = (chunk + 31) & ~(size_t)31;
+inline size_t bin_chunks(size_t P) {  // must match make_bin_plan (binning.cuh): power-of-two chunks >= 1024
+  size_t chunk = 1024;
+  while (chunk * 1024 < P) chunk <<= 1;
   return P ? (P + chunk - 1) / chunk : 0;
 }
 
 inline size_t geom_bytes(size_t P) {
-  return 3 * align_up(16 * P) + 4 * align_up(4 * P) + align_up(4 * 256 * (sort_ctas(P) + 1)) + ALIGN;
+  return 3 * align_up(16 * P) + 4 * align_up(4 * P) + align_up(4 * 256 * (sort_ctas(P) + 1)) + align_up(8 * P) + ALIGN;
 }
 inline GeomView geom_view(void* base, size_t P) {
   char* p = (char*)base;
@@ -102,7 +103,8 @@ inline GeomView geom_view(void* base, size_t P) {
   v.keys[1] = (uint32_t*)p; p += align_up(4 * P);
   v.vals[0] = (uint32_t*)p; p += align_up(4 * P);
   v.vals[1] = (uint32_t*)p; p += align_up(4 * P);
-  v.cta_hist = (uint32_t*)p;
+  v.cta_hist = (uint32_t*)p; p += align_up(4 * 256 * (sort_ctas(P) + 1));
+  v.rects = (uint2*)p;
   return v;
 }
 inline size_t image_bytes(size_t N, size_t T, size_t P) {

@@ -268,13 +268,22 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   }
   {
   ScopedStage prof_(GSR_STAGE_BIN_COUNT, stream);
-  // order-preserving binning, counting half
-  const int tasks = plan.n_chunks * plan.n_bands;
-  const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
-  GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
-           "bin_pass smem attribute");
-  bin_pass_kernel<false><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
-      in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, nullptr);
+  if (bin_parallel(T, plan)) {
+    // parallel binning, counting half: one CTA per chunk, all tiles in shared memory
+    const size_t smem = binc_smem(cam.gx, cam.gy);
+    GSR_CUDA(cudaFuncSetAttribute(bin_count_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+             "bin_count smem attribute");
+    bin_count_cta_kernel<<<dim3(plan.n_chunks, BINC_BANDS), BINC_THREADS, smem, stream>>>(
+        in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan.chunk, g.rects, im.matrix);
+  } else {
+    // order-preserving serial walk (tile grids too large for a shared-memory table), counting half
+    const int tasks = plan.n_chunks * plan.n_bands;
+    const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
+    GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
+             "bin_pass smem attribute");
+    bin_pass_kernel<false><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
+        in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, nullptr, nullptr);
+  }
   GSR_STAGE("bin_count", in->debug, stream);
   column_scan_kernel<<<((int)T + 31) / 32, 1024, 0, stream>>>(im.matrix, plan.n_chunks, (int)T, im.tile_count);
   GSR_STAGE("column_scan", in->debug, stream);
@@ -309,13 +318,17 @@ int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void
   if (R > 0) {
     ScopedStage prof_(GSR_STAGE_BIN_SCATTER, stream);
     const BinPlan plan = make_bin_plan(in->P, cam.gx, cam.gy);
-    const int tasks = plan.n_chunks * plan.n_bands;
-    const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
-    GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
-             "bin_pass smem attribute");
-    bin_pass_kernel<true><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
-        in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list);
-    GSR_STAGE("bin_scatter", in->debug, stream);
+    {
+      // order-preserving walk; when the parallel count ran it left the clipped rectangles in depth order
+      const int tasks = plan.n_chunks * plan.n_bands;
+      const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
+      GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
+               "bin_pass smem attribute");
+      bin_pass_kernel<true><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
+          in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list,
+          bin_parallel(T, plan) ? g.rects : nullptr);
+      GSR_STAGE("bin_scatter", in->debug, stream);
+    }
   }
   ScopedStage prof_(GSR_STAGE_RENDER_FWD, stream);
   dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
