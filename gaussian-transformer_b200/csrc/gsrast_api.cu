@@ -14,6 +14,7 @@
 #include "binning.cuh"
 #include "common.cuh"
 #include "depth_sort.cuh"
+#include "knn.cuh"
 #include "preprocess_bwd.cuh"
 #include "preprocess_fwd.cuh"
 #include "render_bwd.cuh"
@@ -427,6 +428,71 @@ int gsr_sh_grad_from_factors(int32_t P, int32_t D, int32_t M, int32_t V, const f
     sh_grad_from_factors_kernel<false><<<blocks, PB_THREADS, 0, stream>>>(P, D, M, V, means3D, campos, factors,
                                                                          dL_dsh, accumulate);
   GSR_STAGE("sh_grad_from_factors", 0, stream);
+  return GSR_OK;
+}
+
+// ---- simple_knn.distCUDA2
+namespace {
+struct KnnView {
+  uint32_t* bounds;
+  uint32_t* keys[2];
+  uint32_t* vals[2];
+  uint32_t* cta_hist;
+  float4* sorted;
+  KnnBox* boxes;
+  KnnBox* supers;
+  size_t bytes;
+};
+KnnView knn_view(void* base, size_t P) {
+  const size_t nb = (P + KNN_BOX - 1) / KNN_BOX, ns = (nb + KNN_SUPER - 1) / KNN_SUPER;
+  char* p = (char*)base;
+  KnnView v;
+  v.bounds = (uint32_t*)p; p += ALIGN;
+  for (int k = 0; k < 2; k++) { v.keys[k] = (uint32_t*)p; p += align_up(4 * P); }
+  for (int k = 0; k < 2; k++) { v.vals[k] = (uint32_t*)p; p += align_up(4 * P); }
+  v.cta_hist = (uint32_t*)p; p += align_up(4 * 256 * (sort_ctas(P) + 1));
+  v.sorted = (float4*)p; p += align_up(16 * P);
+  v.boxes = (KnnBox*)p; p += align_up(sizeof(KnnBox) * nb);
+  v.supers = (KnnBox*)p; p += align_up(sizeof(KnnBox) * ns);
+  v.bytes = (size_t)(p - (char*)base) + ALIGN;
+  return v;
+}
+}  // namespace
+
+int gsr_knn_scratch_bytes(int32_t P, size_t* bytes) {
+  if (P < 0 || !bytes) return fail(GSR_ERR_INVALID, "gsr_knn_scratch_bytes: bad arguments");
+  *bytes = knn_view(nullptr, (size_t)P).bytes;
+  return GSR_OK;
+}
+
+int gsr_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scratch, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0) return fail(GSR_ERR_INVALID, "gsr_knn_dist2: P < 0");
+  if (P == 0) return GSR_OK;
+  if (!points || !mean_dist2 || !scratch) return fail(GSR_ERR_INVALID, "gsr_knn_dist2: NULL pointer");
+  KnnView v = knn_view(scratch, (size_t)P);
+  const int blocks = (P + 255) / 256;
+  GSR_CUDA(cudaMemsetAsync(v.bounds, 0xff, 12, stream), "knn memset min");
+  GSR_CUDA(cudaMemsetAsync(v.bounds + 3, 0x00, 12, stream), "knn memset max");
+  knn_bounds_kernel<<<blocks < 592 ? blocks : 592, 256, 0, stream>>>(P, points, v.bounds);
+  knn_morton_kernel<<<blocks, 256, 0, stream>>>(P, points, v.bounds, v.keys[0]);
+  GSR_STAGE("knn_morton", 0, stream);
+  const int n_cta = (int)sort_ctas((size_t)P);
+  for (int pass = 0; pass < 4; pass++) {  // 30-bit codes: 4 stable 8-bit passes, result in keys[0] / vals[0]
+    const int src = pass & 1, dst = src ^ 1, shift = 8 * pass;
+    radix_hist_kernel<<<n_cta, RS_THREADS, 0, stream>>>(v.keys[src], P, shift, n_cta, v.cta_hist);
+    uint32_t* digit_total = v.cta_hist + (size_t)256 * n_cta;
+    radix_rowscan_kernel<<<256, 256, 0, stream>>>(v.cta_hist, n_cta, digit_total);
+    radix_scatter_kernel<<<n_cta, RS_THREADS, 0, stream>>>(v.keys[src], pass == 0 ? nullptr : v.vals[src], P, shift,
+                                                          n_cta, v.cta_hist, digit_total, v.keys[dst], v.vals[dst]);
+  }
+  GSR_STAGE("knn_sort", 0, stream);
+  const int nb = (P + KNN_BOX - 1) / KNN_BOX, ns = (nb + KNN_SUPER - 1) / KNN_SUPER;
+  knn_gather_kernel<<<blocks, 256, 0, stream>>>(P, points, v.vals[0], v.sorted);
+  knn_boxes_kernel<<<nb, KNN_BOX, 0, stream>>>(P, v.sorted, v.boxes);
+  knn_supers_kernel<<<ns, 32, 0, stream>>>(nb, v.boxes, v.supers);
+  knn_search_kernel<<<nb, KNN_BOX, 0, stream>>>(P, v.sorted, nb, v.boxes, ns, v.supers, mean_dist2);
+  GSR_STAGE("knn_search", 0, stream);
   return GSR_OK;
 }
 

@@ -153,6 +153,14 @@ GSR_API int gsr_sh_grad_from_factors(int32_t P, int32_t D, int32_t M, int32_t V,
                                      const float* campos, const float* factors, float* dL_dsh,
                                      int32_t accumulate, void* stream);
 
+/* Mean squared distance to the 3 nearest neighbours of every point: replaces SimpleKNN::knn / distCUDA2
+ * (submodules/simple-knn/simple_knn.cu:185-221, spatial.cu:15-26), which scene/gaussian_model.py:134 calls to
+ * initialise the Gaussian scales.  Exact 3-NN with the reference's distance arithmetic: results are bit-identical.
+ *   points      float[P*3] device     mean_dist2  float[P] device out
+ *   scratch     gsr_knn_scratch_bytes(P) bytes of device memory. */
+GSR_API int gsr_knn_scratch_bytes(int32_t P, size_t* bytes);
+GSR_API int gsr_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scratch, void* stream);
+
 /* present[i] = (view-space z > 0.2).  Replaces Rasterizer::markVisible /
  * checkFrustum (DGR/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153). */
 GSR_API int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,

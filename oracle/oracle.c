@@ -791,3 +791,29 @@ int orc_num_threads(void) {
   return 1;
 #endif
 }
+
+/* ------------------------------------------------------------------------------------------------------------
+ * simple_knn: mean squared distance to the 3 nearest neighbours (submodules/simple-knn/simple_knn.cu:130-183).
+ * The reference's search is exact, so a brute-force scan with its distance arithmetic -- FFMA(dz, dz, FFMA(dx,
+ * dx, dy*dy)) with d = other - point (:132-133 as compiled; pinned by tests/golden/data/c1_knn_ref.npy) -- its strict-less insertion (:136-143) and
+ * (best0 + best1 + best2) / 3 (:181) gives the same bits.  O(P^2): test sizes only. */
+void orc_knn3(int P, const float* pts, float* out) {
+#pragma omp parallel for schedule(static)
+  for (int i = 0; i < P; i++) {
+    const float x = pts[3 * i], y = pts[3 * i + 1], z = pts[3 * i + 2];
+    float best[3] = {3.402823466e+38F, 3.402823466e+38F, 3.402823466e+38F};
+    for (int j = 0; j < P; j++) {
+      if (j == i) continue;
+      const float dx = pts[3 * j] - x, dy = pts[3 * j + 1] - y, dz = pts[3 * j + 2] - z;
+      float dist = fmaf(dz, dz, fmaf(dx, dx, dy * dy));
+      for (int k = 0; k < 3; k++) {
+        if (best[k] > dist) {
+          const float t = best[k];
+          best[k] = dist;
+          dist = t;
+        }
+      }
+    }
+    out[i] = ((best[0] + best[1]) + best[2]) / 3.0f;
+  }
+}

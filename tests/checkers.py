@@ -15,6 +15,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 ORACLE_SO = os.path.join(ROOT, "oracle", "_build", "liboracle.so")
 REF_SO = os.path.join(ROOT, "oracle", "_ref", "libref_rasterizer.so")
+REF_KNN_SO = os.path.join(ROOT, "oracle", "_ref", "libref_knn.so")
 
 _c = ctypes
 _fp = _c.POINTER(_c.c_float)
@@ -139,6 +140,27 @@ class Oracle:
 
     def higher_msb(self, n):
         return int(self.lib.orc_higher_msb(n))
+
+    def knn3(self, points):
+        """(P,) mean squared distance to the 3 nearest neighbours, brute force (oracle.c orc_knn3)."""
+        pts = _np_f(points)
+        out = np.zeros(len(pts), dtype=np.float32)
+        self.lib.orc_knn3.argtypes = [_c.c_int, _c.c_void_p, _c.c_void_p]
+        self.lib.orc_knn3(len(pts), _p(pts), _p(out))
+        return out
+
+
+def ref_knn(points):
+    """The UNMODIFIED reference simple_knn (oracle/_ref/libref_knn.so) on a CUDA tensor (P,3) -> (P,) tensor."""
+    import torch
+    lib = _c.CDLL(REF_KNN_SO)
+    lib.ref_knn.argtypes = [_c.c_int, _c.c_void_p, _c.c_void_p]
+    pts = points.to(torch.float32).contiguous()
+    out = torch.zeros(pts.shape[0], dtype=torch.float32, device=pts.device)
+    torch.cuda.synchronize()
+    rc = lib.ref_knn(pts.shape[0], pts.data_ptr(), out.data_ptr())
+    assert rc == 0, f"reference simple_knn failed: cuda error {rc}"
+    return out
 
 
 class _RefViews(_c.Structure):

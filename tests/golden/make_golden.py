@@ -62,6 +62,10 @@ def main():
     os.makedirs(out, exist_ok=True)
     ref = Reference()
     digest(ref, "c1_tiramisu", out)
+    # the reference simple_knn on config 1's points (pins oracle.c orc_knn3, tests/test_cpu_knn.py)
+    from checkers import ref_knn
+    xyz = np.load(os.path.join(HERE, "data", "c1_tiramisu_points.npz"))["xyz"]
+    np.save(os.path.join(out, "c1_knn_ref.npy"), ref_knn(torch.from_numpy(xyz).cuda()).cpu().numpy())
     if len(sys.argv) > 2 and sys.argv[2] == "digest-only":
         return
     for name in cases.GOLDEN:

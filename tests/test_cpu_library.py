@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def test_library_exports_every_declared_symbol():
     from diff_gaussian_rasterization import _lib
     hdr = open(os.path.join(ROOT, "include", "gsrast.h")).read()
-    declared = set(re.findall(r"\b(gsr_[a-z_]+)\s*\(", hdr))
+    declared = set(re.findall(r"\b(gsr_[a-z0-9_]+)\s*\(", hdr))
     assert declared == set(_lib.EXPORTS), declared ^ set(_lib.EXPORTS)
     for name in declared:
         assert hasattr(_lib.lib, name), name
