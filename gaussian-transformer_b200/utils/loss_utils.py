@@ -1,0 +1,92 @@
+"""`utils.loss_utils`: the reference's training loss (utils/loss_utils.py) on the library's fused kernels.
+
+Same names and argument meaning as the reference module -- `l1_loss`, `l2_loss`, `ssim` -- plus `l1_ssim_loss`,
+the train.py:91-92 combination in ONE forward+backward pair of launches (csrc/loss.cuh):
+
+    Ll1  = l1_loss(image, gt_image)
+    loss = (1.0 - opt.lambda_dssim) * Ll1 + opt.lambda_dssim * (1.0 - ssim(image, gt_image))
+  becomes
+    loss, Ll1 = l1_ssim_loss(image, gt_image, opt.lambda_dssim)
+
+CUDA float32 only; there is no CPU path.  The second image is the ground truth: it receives no gradient.
+"""
+import ctypes
+
+import torch
+
+from diff_gaussian_rasterization import _lib
+
+
+def _check(img, gt):
+    if not (img.is_cuda and gt.is_cuda):
+        raise RuntimeError("loss_utils: tensors must be CUDA tensors (there is no CPU path)")
+    if img.shape != gt.shape or img.dim() not in (3, 4):
+        raise RuntimeError("loss_utils: images must have the same (C,H,W) or (B,C,H,W) shape")
+    if gt.requires_grad:
+        raise RuntimeError("loss_utils: the second image is the ground truth and gets no gradient")
+
+
+def _launch(img, gt, lam, want_grad):
+    """img, gt: contiguous float32 (C,H,W).  Returns (out3 tensor [L1, SSIM, loss], d loss / d img or None)."""
+    C, H, W = img.shape
+    dev = img.device
+    out3 = torch.empty(3, dtype=torch.float32, device=dev)
+    grad = torch.empty_like(img) if want_grad else None
+    with torch.cuda.device(dev):
+        nbytes = ctypes.c_size_t()
+        _lib.check(_lib.lib.gsr_loss_scratch_bytes(C, H, W, ctypes.byref(nbytes)))
+        scratch = torch.empty(nbytes.value, dtype=torch.uint8, device=dev)
+        _lib.check(_lib.lib.gsr_l1_ssim_loss(C, H, W, img.data_ptr(), gt.data_ptr(), float(lam), out3.data_ptr(),
+                                             grad.data_ptr() if want_grad else None, scratch.data_ptr(),
+                                             torch.cuda.current_stream(dev).cuda_stream))
+    return out3, grad
+
+
+class _L1SSIM(torch.autograd.Function):
+    """out3 = [L1, SSIM, (1-l)*L1 + l*(1-SSIM)]; only out3[2] carries a gradient (the others are reports)."""
+
+    @staticmethod
+    def forward(ctx, img, gt, lam):
+        x = img.detach().to(torch.float32).contiguous()
+        y = gt.detach().to(torch.float32).contiguous()
+        shape = x.shape
+        if x.dim() == 4:  # the mean over everything is the same with batch folded into channels
+            x, y = x.reshape(-1, *shape[2:]), y.reshape(-1, *shape[2:])
+        out3, grad = _launch(x, y, lam, ctx.needs_input_grad[0])
+        ctx.save_for_backward(grad.reshape(shape) if grad is not None else None)
+        return out3
+
+    @staticmethod
+    def backward(ctx, g_out):
+        (grad,) = ctx.saved_tensors
+        return (grad * g_out[2] if grad is not None else None), None, None
+
+
+def l1_ssim_loss(image, gt_image, lambda_dssim=0.2):
+    """(loss, Ll1): train.py:91-92 in one fused forward + backward.  `Ll1` is detached (train.py only logs it)."""
+    _check(image, gt_image)
+    out3 = _L1SSIM.apply(image, gt_image, float(lambda_dssim))
+    return out3[2], out3[0].detach()
+
+
+def l1_loss(network_output, gt):
+    """utils/loss_utils.py:17-18."""
+    _check(network_output, gt)
+    return _L1SSIM.apply(network_output, gt, 0.0)[2]
+
+
+def l2_loss(network_output, gt):
+    """utils/loss_utils.py:20-21 (unused by the trainers; plain torch)."""
+    return ((network_output - gt) ** 2).mean()
+
+
+def ssim(img1, img2, window_size=11, size_average=True):
+    """utils/loss_utils.py:33-63: 11x11 Gaussian window, sigma 1.5, zero padding, per channel."""
+    if window_size != 11:
+        raise RuntimeError("ssim: only the reference's window_size = 11 is built")
+    _check(img1, img2)
+    if size_average:
+        return 1.0 - _L1SSIM.apply(img1, img2, 1.0)[2]
+    if img1.dim() != 4:
+        raise RuntimeError("ssim: size_average=False needs a (B,C,H,W) batch")  # the reference's .mean(1) x3
+    return torch.stack([1.0 - _L1SSIM.apply(img1[b], img2[b], 1.0)[2] for b in range(img1.size(0))])

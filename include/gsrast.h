@@ -161,6 +161,19 @@ GSR_API int gsr_sh_grad_from_factors(int32_t P, int32_t D, int32_t M, int32_t V,
 GSR_API int gsr_knn_scratch_bytes(int32_t P, size_t* bytes);
 GSR_API int gsr_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scratch, void* stream);
 
+/* Fused training loss on the rendered image and its gradient, the dL/dpixel that gsr_backward consumes:
+ *   L1 = mean |img - gt|                                   utils/loss_utils.py:17-18
+ *   SSIM: 11x11 Gaussian window (sigma 1.5), zero padding, per channel, mean          :24-63
+ *   loss = (1 - lambda) * L1 + lambda * (1 - SSIM)                                     train.py:91-92
+ * replacing five depthwise convolutions, ~15 elementwise kernels and their autograd replay by two passes.
+ *   img, gt   float[C*H*W] device (gt gets no gradient)
+ *   out3      float[3] device out: L1, SSIM, loss
+ *   dL_dimg   float[C*H*W] device out, d loss / d img (NULL: values only)
+ *   scratch   gsr_loss_scratch_bytes(C, H, W) bytes. */
+GSR_API int gsr_loss_scratch_bytes(int32_t C, int32_t H, int32_t W, size_t* bytes);
+GSR_API int gsr_l1_ssim_loss(int32_t C, int32_t H, int32_t W, const float* img, const float* gt,
+                             float lambda_dssim, float* out3, float* dL_dimg, void* scratch, void* stream);
+
 /* present[i] = (view-space z > 0.2).  Replaces Rasterizer::markVisible /
  * checkFrustum (DGR/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153). */
 GSR_API int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,

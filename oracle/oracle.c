@@ -817,3 +817,86 @@ void orc_knn3(int P, const float* pts, float* out) {
     out[i] = ((best[0] + best[1]) + best[2]) / 3.0f;
   }
 }
+
+/* ---- training loss: (1 - lambda) * L1 + lambda * (1 - SSIM)      
+ * utils/loss_utils.py:17-18 (l1_loss), :23-31 (the 11x11 window: outer product of the float32 1-D Gaussian,
+ * rounded to float32), :43-63 (_ssim: five zero-padded depthwise convolutions, C1 = 0.01^2, C2 = 0.03^2, mean),
+ * combined as train.py:91-92.  Direct 121-tap sums in double, and the analytic gradient w.r.t. img (the same
+ * chain autograd replays: dS/dmu1, dS/dE[x^2], dS/dE[xy] maps pushed back through the symmetric window).
+ * Pinned by tests/golden/data/loss_*.npz, which hold the reference module's own outputs and autograd gradients.
+ *   out3 = {L1, SSIM, loss};  dL_dimg float[C*H*W] (may be NULL). */
+void orc_l1_ssim(int C, int H, int W, const float* img, const float* gt, double lambda, double* out3,
+                 float* dL_dimg) {
+  float g1[11];
+  {
+    float e[11], s = 0.f; /* torch.Tensor([...]) is float32; gauss / gauss.sum() in float32 */
+    for (int k = 0; k < 11; k++) e[k] = (float)exp(-(double)((k - 5) * (k - 5)) / (2.0 * 1.5 * 1.5));
+    for (int k = 0; k < 11; k++) s += e[k];
+    for (int k = 0; k < 11; k++) g1[k] = e[k] / s;
+  }
+  double w2[11][11];
+  for (int i = 0; i < 11; i++)
+    for (int j = 0; j < 11; j++) w2[i][j] = (double)(float)(g1[i] * g1[j]);
+  const size_t plane = (size_t)H * W, n = (size_t)C * plane;
+  double* maps = (double*)malloc(3 * n * sizeof(double));
+  double sum_abs = 0.0, sum_ssim = 0.0;
+  const double C1 = 0.01 * 0.01, C2 = 0.03 * 0.03;
+  for (int c = 0; c < C; c++) {
+    const float* x = img + c * plane;
+    const float* y = gt + c * plane;
+#pragma omp parallel for schedule(static) reduction(+ : sum_abs, sum_ssim)
+    for (int py = 0; py < H; py++)
+      for (int px = 0; px < W; px++) {
+        double m1 = 0, m2 = 0, e11 = 0, e22 = 0, e12 = 0;
+        for (int i = 0; i < 11; i++) {
+          const int yy = py + i - 5;
+          if (yy < 0 || yy >= H) continue;
+          for (int j = 0; j < 11; j++) {
+            const int xx = px + j - 5;
+            if (xx < 0 || xx >= W) continue;
+            const double a = x[(size_t)yy * W + xx], b = y[(size_t)yy * W + xx], w = w2[i][j];
+            m1 += w * a; m2 += w * b; e11 += w * a * a; e22 += w * b * b; e12 += w * a * b;
+          }
+        }
+        const double s11 = e11 - m1 * m1, s22 = e22 - m2 * m2, s12 = e12 - m1 * m2;
+        const double A1 = 2 * m1 * m2 + C1, A2 = 2 * s12 + C2, B1 = m1 * m1 + m2 * m2 + C1, B2 = s11 + s22 + C2;
+        const double S = A1 * A2 / (B1 * B2);
+        sum_ssim += S;
+        sum_abs += fabs((double)x[(size_t)py * W + px] - (double)y[(size_t)py * W + px]);
+        const size_t o = c * plane + (size_t)py * W + px;
+        /* partials in (mu1, E11, E12), the sigmas expanded: s11 = E11 - mu1^2, s12 = E12 - mu1 mu2 */
+        const double dS_dA1 = A2 / (B1 * B2), dS_dA2 = A1 / (B1 * B2), dS_dB1 = -S / B1, dS_dB2 = -S / B2;
+        maps[o] = dS_dA1 * 2 * m2 + dS_dA2 * (-2 * m2) + dS_dB1 * 2 * m1 + dS_dB2 * (-2 * m1);
+        maps[n + o] = dS_dB2;
+        maps[2 * n + o] = 2 * dS_dA2;
+      }
+  }
+  const double l1 = sum_abs / (double)n, ss = sum_ssim / (double)n;
+  out3[0] = l1;
+  out3[1] = ss;
+  out3[2] = (1.0 - lambda) * l1 + lambda * (1.0 - ss);
+  if (dL_dimg) {
+    for (int c = 0; c < C; c++) {
+#pragma omp parallel for schedule(static)
+      for (int py = 0; py < H; py++)
+        for (int px = 0; px < W; px++) {
+          double a = 0, b = 0, d = 0;
+          for (int i = 0; i < 11; i++) {
+            const int yy = py + i - 5;
+            if (yy < 0 || yy >= H) continue;
+            for (int j = 0; j < 11; j++) {
+              const int xx = px + j - 5;
+              if (xx < 0 || xx >= W) continue;
+              const size_t o = c * plane + (size_t)yy * W + xx;
+              a += w2[i][j] * maps[o]; b += w2[i][j] * maps[n + o]; d += w2[i][j] * maps[2 * n + o];
+            }
+          }
+          const size_t o = c * plane + (size_t)py * W + px;
+          const double xv = img[o], yv = gt[o], df = xv - yv;
+          const double sgn = df > 0 ? 1.0 : (df < 0 ? -1.0 : 0.0);
+          dL_dimg[o] = (float)((1.0 - lambda) / (double)n * sgn - lambda / (double)n * (a + 2 * xv * b + yv * d));
+        }
+    }
+  }
+  free(maps);
+}

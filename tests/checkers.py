@@ -141,6 +141,18 @@ class Oracle:
     def higher_msb(self, n):
         return int(self.lib.orc_higher_msb(n))
 
+    def l1_ssim(self, img, gt, lambda_dssim, grad=True):
+        """(L1, SSIM, loss) as float64 and d loss / d img (oracle.c orc_l1_ssim).  img, gt: (C,H,W) float32."""
+        img, gt = _np_f(img), _np_f(gt)
+        C, H, W = img.shape
+        out3 = np.zeros(3, dtype=np.float64)
+        g = np.zeros_like(img) if grad else None
+        self.lib.orc_l1_ssim.argtypes = [_c.c_int, _c.c_int, _c.c_int, _c.c_void_p, _c.c_void_p, _c.c_double,
+                                         _c.c_void_p, _c.c_void_p]
+        self.lib.orc_l1_ssim.restype = None
+        self.lib.orc_l1_ssim(C, H, W, _p(img), _p(gt), float(lambda_dssim), _p(out3), _p(g))
+        return out3, g
+
     def knn3(self, points):
         """(P,) mean squared distance to the 3 nearest neighbours, brute force (oracle.c orc_knn3)."""
         pts = _np_f(points)
