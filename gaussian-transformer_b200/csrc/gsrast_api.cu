@@ -500,7 +500,7 @@ int gsr_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scrat
 // ---- fused L1 + SSIM training loss
 int gsr_loss_scratch_bytes(int32_t C, int32_t H, int32_t W, size_t* bytes) {
   if (C <= 0 || H <= 0 || W <= 0 || !bytes) return fail(GSR_ERR_INVALID, "gsr_loss_scratch_bytes: bad arguments");
-  *bytes = ALIGN + align_up((size_t)3 * C * H * W * sizeof(float));
+  *bytes = align_up(LOSS_SLOTS * sizeof(LossAcc)) + align_up((size_t)3 * C * H * W * sizeof(float));
   return GSR_OK;
 }
 
@@ -511,15 +511,15 @@ int gsr_l1_ssim_loss(int32_t C, int32_t H, int32_t W, const float* img, const fl
   if (C > 65535) return fail(GSR_ERR_INVALID, "gsr_l1_ssim_loss: more than 65535 channels");
   if (!img || !gt || !out3 || !scratch) return fail(GSR_ERR_INVALID, "gsr_l1_ssim_loss: NULL pointer");
   LossAcc* acc = (LossAcc*)scratch;
-  float* maps = (float*)((char*)scratch + ALIGN);
-  GSR_CUDA(cudaMemsetAsync(acc, 0, sizeof(LossAcc), stream), "loss memset");
+  float* maps = (float*)((char*)scratch + align_up(LOSS_SLOTS * sizeof(LossAcc)));
+  GSR_CUDA(cudaMemsetAsync(acc, 0, LOSS_SLOTS * sizeof(LossAcc), stream), "loss memset");
   const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
-  loss_pass1_kernel<<<grid, LT * LT, 0, stream>>>(H, W, img, gt, maps, acc);
+  loss_pass1_kernel<<<grid, LOSS_THREADS, 0, stream>>>(H, W, img, gt, maps, acc);
   GSR_STAGE("loss_pass1", 0, stream);
   const double n = (double)C * H * W;
   loss_finish_kernel<<<1, 1, 0, stream>>>(acc, n, lambda_dssim, out3);
   if (dL_dimg) {
-    loss_pass2_kernel<<<grid, LT * LT, 0, stream>>>(H, W, img, gt, maps, (float)((1.0 - lambda_dssim) / n),
+    loss_pass2_kernel<<<grid, LOSS_THREADS, 0, stream>>>(H, W, img, gt, maps, (float)((1.0 - lambda_dssim) / n),
                                                     (float)(lambda_dssim / n), dL_dimg);
     GSR_STAGE("loss_pass2", 0, stream);
   }

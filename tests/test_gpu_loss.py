@@ -21,7 +21,7 @@ def _torch_loss(img, gt, lam):
     """utils/loss_utils.py:17-18, :23-63 and train.py:91-92 in plain torch fp32 (fp32 reference for this kernel)."""
     w = torch.from_numpy(np.load(os.path.join(DATA, "loss_window.npy"))).to(img.device)
     C = img.size(-3)
-    win = (w[:, None] @ w[None, :]).expand(C, 1, 11, 11).contiguous()
+    win = (w[:, None] @ w[None, :]).to(img.dtype).expand(C, 1, 11, 11).contiguous()
     conv = lambda t: F.conv2d(t, win, padding=5, groups=C)
     mu1, mu2 = conv(img), conv(gt)
     s11, s22, s12 = conv(img * img) - mu1 * mu1, conv(gt * gt) - mu2 * mu2, conv(img * gt) - mu1 * mu2
@@ -100,8 +100,9 @@ def test_errors():
         l1_ssim_loss(a.cuda(), torch.rand(3, 8, 9).cuda())
 
 
-def test_1080p_vs_torch_fp32():
-    """BASELINE.json's full image size: the kernel vs the reference formula in torch fp32 (no TF32)."""
+def test_1080p_vs_torch():
+    """BASELINE.json's full image size.  The reference formula in torch fp32 is itself 1.4e-4 of max away from
+    its fp64 evaluation here (sigma = E[x^2] - mu^2 cancels), so fp64 is the truth and fp32 torch the yardstick."""
     from utils.loss_utils import l1_ssim_loss
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
@@ -115,8 +116,14 @@ def test_1080p_vs_torch_fp32():
     loss, l1 = l1_ssim_loss(a, gt, 0.2)
     loss.backward()
     b = img.clone().requires_grad_(True)
-    want, want_l1, _ = _torch_loss(b[None], gt[None], 0.2)
+    ref32, _, _ = _torch_loss(b[None], gt[None], 0.2)
+    ref32.backward()
+    c = img.double().requires_grad_(True)
+    want, want_l1, _ = _torch_loss(c[None], gt.double()[None], 0.2)
     want.backward()
-    np.testing.assert_allclose(l1.item(), want_l1.item(), rtol=2e-5)
-    np.testing.assert_allclose(loss.item(), want.item(), rtol=2e-5)
-    assert (a.grad - b.grad).abs().max().item() <= GRAD_TOL * b.grad.abs().max().item()
+    np.testing.assert_allclose(l1.item(), want_l1.item(), rtol=VAL_RTOL)
+    np.testing.assert_allclose(loss.item(), want.item(), rtol=VAL_RTOL)
+    gmax = c.grad.abs().max().item()
+    err = (a.grad - c.grad).abs().max().item()
+    assert err <= GRAD_TOL * gmax
+    assert err <= 1.25 * (b.grad - c.grad).abs().max().item()   # no farther from fp64 than the reference formula
