@@ -109,6 +109,17 @@ def algorithmic_bytes(P, V, R, N, K, M):
     return a_fwd + a_bwd, per_stage
 
 
+# dram__bytes_read.sum + dram__bytes_write.sum per launch on the C2 workload, from the `ncu --set full` capture
+# summarised in profiles/r01_ncu_full_metrics.txt (a property of the workload, not of the run: bench.py only ever
+# runs C2).  Below the algorithmic bytes wherever list entries and per-Gaussian records are re-read from the L2.
+NCU_DRAM_BYTES_C2 = {
+    "preprocess_fwd": 216.99e6 + 42.09e6,
+    "render_fwd": 65.83e6 + 18.19e6,
+    "render_bwd": 116.69e6 + 6.54e6,
+    "preprocess_bwd": 285.00e6 + 241.79e6,
+}
+
+
 def make_scene(rank, world):
     import gsr_scenes as S
     yaw = 0.0 if world == 1 else -15.0 + 30.0 * rank / (world - 1)
@@ -325,7 +336,8 @@ def run_ours(args, rank, world, local_rank):
                 "ms_per_step": ms_e2e},
         "gpu_launches": kernels_per_step * args.steps,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "peak_kind": peak_kind,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_C2.get(dom),
+                     "traffic_source": "profiles/r01_ncu_full_metrics.txt (ncu --set full, same workload)",
                      "algorithmic_bytes": a_stage[dom], "kernel_ms": dom_ms,
                      "note": "alpha blending is FP32/MUFU-pipe bound, not HBM bound; the HBM fraction is reported "
                              "because BASELINE.json's metric asks for it"},
