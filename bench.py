@@ -37,6 +37,7 @@ def parse():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~10-20 s CPU oracle timing")
+    ap.add_argument("--timeline", default=None, help="dev: write a kernel timeline of 2 steps (torch.profiler) and exit")
     ap.add_argument("--dp-exchange", default="factors", choices=("factors", "allreduce"),
                     help="N > 1: all-gather 12 B/Gaussian SH factors + all-reduce 44 B/Gaussian (default), or "
                          "all-reduce the full 236 B/Gaussian")
@@ -208,6 +209,7 @@ def run_ours(args, rank, world, local_rank):
         import gsr_dp
         keep = LEAVES if args.dp_exchange == "allreduce" else gsr_dp.SMALL_LEAVES
         flat = gsr_dp.FlatGrads({k: tuple(t[k].shape) for k in keep}, dev)
+        exchange = gsr_dp.FactorExchange(1, P_GAUSS, dev, world) if args.dp_exchange == "factors" else None
 
     def render_backward(src):
         leaves = {k: src[k].detach().requires_grad_(True) for k in LEAVES}
@@ -227,16 +229,17 @@ def run_ours(args, rank, world, local_rank):
         box = {}
         if args.dp_exchange == "allreduce":
             def rb(_v):
-                box["loss"], g = render_backward(src)
+                with gsr_dp.grads_into(flat):
+                    box["loss"], g = render_backward(src)
                 return g
             g = gsr_dp.dp_step(rb, world, flat, rank, world)
         else:
-            def rb(_v):
-                with gsr_dp.capture_sh_factors() as items:
+            def rb(_v, _ex):
+                with gsr_dp.capture_sh_factors(exchange), gsr_dp.grads_into(flat):
                     box["loss"], g = render_backward(src)
-                g["sh_factor"] = items[0]
                 return g
-            g = gsr_dp.dp_step_factored(rb, world, flat, rank, world, src["means3D"], SH_DEG, M_COEF)
+            g = gsr_dp.dp_step_factored(rb, world, flat, rank, world, src["means3D"], SH_DEG, M_COEF,
+                                        exchange=exchange)
         return box["loss"], [g[k] for k in LEAVES]
 
     def sync_all():
@@ -247,6 +250,20 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(max(args.warmup, 3)):
         step(t)
     sync_all()
+    if args.timeline:
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as tp:
+            for _ in range(2):
+                step(t)
+            sync_all()
+        if rank == 0:
+            ev = sorted((e for e in tp.events() if e.device_type.name == "CUDA"), key=lambda e: e.time_range.start)
+            t0 = ev[0].time_range.start
+            with open(args.timeline, "w") as f:
+                for e in ev:
+                    f.write("%9.1f %8.1f  %s\n" % (e.time_range.start - t0, e.time_range.end - e.time_range.start,
+                                                    e.name[:90]))
+        return None
     # ---- timed region 1: inputs resident in HBM ("value"); per-stage device times recorded by the library
     clocks = ClockSampler(local_rank) if rank == 0 else None
     _lib.profile_enable(True)
@@ -377,7 +394,10 @@ def main():
     if world > 1:
         import torch.distributed as dist
         torch.cuda.set_device(local_rank)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        # high-priority NCCL stream: the SH-factor all-gather is launched between the two backward stages and must
+        # get SMs while preprocess_bwd's CTAs are still being dispatched
+        opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank), pg_options=opts)
     line = run_ours(args, rank, world, local_rank)
     if line is not None:
         print(json.dumps(line), flush=True)

@@ -340,18 +340,14 @@ int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void
   return GSR_OK;
 }
 
-int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, const void* binning,
-                 const void* image, int64_t R, const float* dL_dpix, float* dL_dmeans3D, float* dL_dmeans2D,
-                 float* dL_dsh, float* dL_dcolors, float* dL_dopacity, float* dL_dscales, float* dL_drotations,
-                 float* dL_dcov3D, float* dL_dconic, void* bwd_scratch, void* stream_) {
+// Backward stage 1: per-pixel alpha-blending backward into the per-Gaussian accumulators of bwd_scratch.
+int gsr_backward_blend(const gsr_inputs* in, const void* geom, const void* binning, const void* image, int64_t R,
+                       const float* dL_dpix, void* bwd_scratch, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (int rc = check_inputs(in)) return rc;
   if (in->P == 0) return GSR_OK;
-  if (!radii || !geom || !image || !dL_dpix || !bwd_scratch || (R > 0 && !binning))
+  if (!geom || !image || !dL_dpix || !bwd_scratch || (R > 0 && !binning))
     return fail(GSR_ERR_INVALID, "gsr_backward: NULL buffer");
-  if (!dL_dmeans3D || !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dscales || !dL_drotations ||
-      !dL_dcov3D || !dL_dconic)
-    return fail(GSR_ERR_INVALID, "gsr_backward: NULL gradient output");
   const Cam cam = make_cam(in);
   const size_t N = (size_t)in->W * in->H, T = (size_t)cam.gx * cam.gy;
   GeomView g = geom_view(const_cast<void*>(geom), (size_t)in->P);
@@ -366,6 +362,24 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
                                                   in->colors_precomp, im.final_T, im.n_contrib, dL_dpix, bw);
     GSR_STAGE("render_bwd", in->debug, stream);
   }
+  return GSR_OK;
+}
+
+// Backward stage 2: accumulators -> gradients of the 3-D parameters (fused preprocess backward).
+int gsr_backward_geometry(const gsr_inputs* in, const int32_t* radii, const void* geom, float* dL_dmeans3D,
+                          float* dL_dmeans2D, float* dL_dsh, float* dL_dcolors, float* dL_dopacity,
+                          float* dL_dscales, float* dL_drotations, float* dL_dcov3D, float* dL_dconic,
+                          void* bwd_scratch, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (int rc = check_inputs(in)) return rc;
+  if (in->P == 0) return GSR_OK;
+  if (!radii || !geom || !bwd_scratch) return fail(GSR_ERR_INVALID, "gsr_backward: NULL buffer");
+  if (!dL_dmeans3D || !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dscales || !dL_drotations ||
+      !dL_dcov3D || !dL_dconic)
+    return fail(GSR_ERR_INVALID, "gsr_backward: NULL gradient output");
+  const Cam cam = make_cam(in);
+  GeomView g = geom_view(const_cast<void*>(geom), (size_t)in->P);
+  BwdView bw = bwd_view(bwd_scratch, (size_t)in->P);
   BwdOut out;
   out.dL_dmeans3D = dL_dmeans3D;
   out.dL_dmeans2D = dL_dmeans2D;
@@ -399,6 +413,33 @@ int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, c
                                                                 cam, radii, g.g2, bw, out);
   }
   GSR_STAGE("preprocess_bwd", in->debug, stream);
+  return GSR_OK;
+}
+
+int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, const void* binning,
+                 const void* image, int64_t R, const float* dL_dpix, float* dL_dmeans3D, float* dL_dmeans2D,
+                 float* dL_dsh, float* dL_dcolors, float* dL_dopacity, float* dL_dscales, float* dL_drotations,
+                 float* dL_dcov3D, float* dL_dconic, void* bwd_scratch, void* stream_) {
+  if (in && in->P > 0 && !radii) return fail(GSR_ERR_INVALID, "gsr_backward: NULL buffer");
+  if (in && in->P > 0 &&
+      (!dL_dmeans3D || !dL_dmeans2D || !dL_dcolors || !dL_dopacity || !dL_dscales || !dL_drotations ||
+       !dL_dcov3D || !dL_dconic))
+    return fail(GSR_ERR_INVALID, "gsr_backward: NULL gradient output");
+  if (int rc = gsr_backward_blend(in, geom, binning, image, R, dL_dpix, bwd_scratch, stream_)) return rc;
+  return gsr_backward_geometry(in, radii, geom, dL_dmeans3D, dL_dmeans2D, dL_dsh, dL_dcolors, dL_dopacity,
+                               dL_dscales, dL_drotations, dL_dcov3D, dL_dconic, bwd_scratch, stream_);
+}
+
+// The view's SH factors straight from the blend accumulators (between the two backward stages).
+int gsr_backward_sh_factors(int32_t P, const void* geom, const void* bwd_scratch, float* factors, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0) return fail(GSR_ERR_INVALID, "gsr_backward_sh_factors: P < 0");
+  if (P == 0) return GSR_OK;
+  if (!geom || !bwd_scratch || !factors) return fail(GSR_ERR_INVALID, "gsr_backward_sh_factors: NULL pointer");
+  GeomView g = geom_view(const_cast<void*>(geom), (size_t)P);
+  BwdView bw = bwd_view(const_cast<void*>(bwd_scratch), (size_t)P);
+  sh_acc_factors_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.g2, bw.acc0, factors);
+  GSR_STAGE("sh_acc_factors", 0, stream);
   return GSR_OK;
 }
 

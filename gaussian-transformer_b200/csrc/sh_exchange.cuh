@@ -26,6 +26,21 @@ __global__ void __launch_bounds__(256) sh_color_factors_kernel(int P, const floa
   factors[3 * I + 2] = (flags & 4u) ? 0.f : dL_dcolors[3 * I + 2];
 }
 
+// The same factors read from the blend accumulators (acc0 = dL_dcolor.rgb, dL_dopacity) between the two backward
+// stages, so that their exchange can start before preprocess_bwd runs.
+__global__ void __launch_bounds__(256) sh_acc_factors_kernel(int P, const float4* __restrict__ g2,
+                                                             const float4* __restrict__ acc0,
+                                                             float* __restrict__ factors) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  const uint32_t flags = __float_as_uint(__ldg(&g2[i].w));
+  const float4 a = __ldg(acc0 + i);
+  const size_t I = (size_t)i;
+  factors[3 * I] = (flags & 1u) ? 0.f : a.x;
+  factors[3 * I + 1] = (flags & 2u) ? 0.f : a.y;
+  factors[3 * I + 2] = (flags & 4u) ? 0.f : a.z;
+}
+
 // dL_dsh[i] (+)= sum_v basis(normalize(mean_i - campos_v)) (x) factors[v][i].  One thread per Gaussian, 48
 // accumulators in registers; STAGED (M == 16, 16-byte aligned output): rows leave through shared memory with
 // coalesced 128-bit stores like preprocess_bwd_staged_kernel.

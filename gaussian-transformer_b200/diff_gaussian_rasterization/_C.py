@@ -103,11 +103,16 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh,
-                                 degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, sh_grad=True):
+                                 degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, sh_grad=True,
+                                 factor_sink=None, out=None):
     """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
 
     sh_grad=False (extension, used by gsr_dp): dL_dsh is not computed and returned as None; the caller rebuilds it
-    from sh_color_factors()/sh_grad_from_factors()."""
+    from the view's SH factors and sh_grad_from_factors().  factor_sink (with sh_grad=False): an object with
+    `buffer(P, device) -> (P,3) float32 tensor` and `emit(campos, factors)`; the factors are written into the buffer
+    BETWEEN the two backward stages and emit() is called there, so that an exchange it launches overlaps the
+    geometry stage.  out (extension): {"means3D" | "sh" | "opacity" | "scales" | "rot": tensor} -- gradients written
+    into the caller's tensors (same shape, float32, contiguous) instead of freshly allocated ones."""
     _check_means(means3D)
     dev = means3D.device
     P = means3D.size(0)
@@ -118,6 +123,12 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
              sh=torch.empty(P, M, 3, **f32) if sh_grad else None,
              colors=torch.empty(P, 3, **f32), opacity=torch.empty(P, 1, **f32), scales=torch.empty(P, 3, **f32),
              rot=torch.empty(P, 4, **f32), cov3D=torch.empty(P, 6, **f32), conic=torch.empty(P, 2, 2, **f32))
+    for k, t in (out or {}).items():
+        if k not in ("means3D", "sh", "opacity", "scales", "rot") or g[k] is None:
+            continue
+        if t.shape != g[k].shape or t.dtype != torch.float32 or t.device != dev or not t.is_contiguous():
+            raise RuntimeError("out[%r] must be a contiguous float32 tensor of shape %s on %s" % (k, tuple(g[k].shape), dev))
+        g[k] = t.view(t.shape)  # a fresh alias: autograd may adopt it as the leaf's .grad without a copy
     if P != 0:
         with torch.cuda.device(dev):
             t = [_f32(x, dev) for x in (background, means3D, sh, colors, None, scales, rotations, cov3D_precomp,
@@ -129,13 +140,33 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             dpix = _f32(dL_dout_color, dev)
             _, _, _, wb = _lib.scratch_bytes(P, int(R), W, H)
             work = torch.empty(wb, dtype=torch.uint8, device=dev)
-            _lib.check(_lib.lib.gsr_backward(
-                ctypes.byref(args), radii.data_ptr(), geomBuffer.data_ptr(),
-                binningBuffer.data_ptr() if binningBuffer.numel() else 0, imageBuffer.data_ptr(), int(R),
-                dpix.data_ptr(), g["means3D"].data_ptr(), g["means2D"].data_ptr(), _ptr(g["sh"]) if (M and sh_grad) else 0,
-                g["colors"].data_ptr(), g["opacity"].data_ptr(), g["scales"].data_ptr(), g["rot"].data_ptr(),
-                g["cov3D"].data_ptr(), g["conic"].data_ptr(), work.data_ptr(),
-                torch.cuda.current_stream(dev).cuda_stream))
+            stream = torch.cuda.current_stream(dev).cuda_stream
+            outs = (g["means3D"].data_ptr(), g["means2D"].data_ptr(), _ptr(g["sh"]) if (M and sh_grad) else 0,
+                    g["colors"].data_ptr(), g["opacity"].data_ptr(), g["scales"].data_ptr(), g["rot"].data_ptr(),
+                    g["cov3D"].data_ptr(), g["conic"].data_ptr())
+            bin_ptr = binningBuffer.data_ptr() if binningBuffer.numel() else 0
+            if factor_sink is None:
+                _lib.check(_lib.lib.gsr_backward(ctypes.byref(args), radii.data_ptr(), geomBuffer.data_ptr(), bin_ptr,
+                                                 imageBuffer.data_ptr(), int(R), dpix.data_ptr(), *outs,
+                                                 work.data_ptr(), stream))
+            else:
+                _lib.check(_lib.lib.gsr_backward_blend(ctypes.byref(args), geomBuffer.data_ptr(), bin_ptr,
+                                                       imageBuffer.data_ptr(), int(R), dpix.data_ptr(),
+                                                       work.data_ptr(), stream))
+                fac = factor_sink.buffer(P, dev)
+                if fac.shape != (P, 3) or fac.dtype != torch.float32 or not fac.is_contiguous():
+                    raise RuntimeError("factor_sink.buffer() must return a contiguous (P,3) float32 tensor")
+                _lib.check(_lib.lib.gsr_backward_sh_factors(P, geomBuffer.data_ptr(), work.data_ptr(),
+                                                            fac.data_ptr(), stream))
+                factor_sink.emit(campos.detach().reshape(3), fac)
+                _lib.check(_lib.lib.gsr_backward_geometry(ctypes.byref(args), radii.data_ptr(),
+                                                          geomBuffer.data_ptr(), *outs, work.data_ptr(), stream))
+    elif factor_sink is not None:
+        factor_sink.emit(campos.detach().reshape(3), factor_sink.buffer(0, dev))
+    if P == 0 and out:
+        for k in out:
+            if g.get(k) is not None:
+                g[k].zero_()
     rasterize_gaussians_backward.last_dL_dconic = g["conic"]  # exposed for the parity tests only
     return (g["means2D"], g["colors"], g["opacity"], g["means3D"], g["cov3D"], g["sh"], g["scales"], g["rot"])
 

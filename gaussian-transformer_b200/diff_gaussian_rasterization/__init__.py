@@ -37,11 +37,29 @@ class GaussianRasterizationSettings(NamedTuple):
     debug: bool
 
 
-# Extension used by gsr_dp (data-parallel over views): while a sink list is installed, the backward of a call
-# that used SHs does not compute dL/dsh (the gradient returned for `shs` is None); it appends
-# (campos, factors (P,3)) of the view to the sink instead, and gsr_dp rebuilds the summed SH gradient after
-# exchanging the factors between ranks.  None (the default) = reference behaviour.
+# Extension used by gsr_dp (data-parallel over views): while a sink is installed, the backward of a call that
+# used SHs does not compute dL/dsh (the gradient returned for `shs` is None); it hands (campos, factors (P,3)) of
+# the view to the sink instead -- BETWEEN the blend and the geometry stage of the backward, so that the exchange
+# the sink launches overlaps the latter -- and gsr_dp rebuilds the summed SH gradient from the exchanged factors.
+# A sink is a list (gets (campos, factors) appended) or an object with buffer(P, device) and emit(campos, factors).
+# None (the default) = reference behaviour.
 _sh_factor_sink = None
+
+
+# Extension used by gsr_dp.grads_into: a dict {"means3D" | "sh" | "opacity" | "scales" | "rot": tensor}; the NEXT
+# backward writes those gradients into the given tensors instead of allocating (consumed by that one call).
+_grad_out = None
+
+
+class _ListSink:
+    def __init__(self, items):
+        self.items = items
+
+    def buffer(self, P, device):
+        return torch.empty(P, 3, dtype=torch.float32, device=device)
+
+    def emit(self, campos, factors):
+        self.items.append((campos, factors))
 
 
 def _snapshot(args, path, note):
@@ -52,6 +70,12 @@ def _snapshot(args, path, note):
         torch.save(cpu, path)
         print(note)
     return write
+
+
+def _take_out():
+    global _grad_out
+    out, _grad_out = _grad_out, None
+    return out
 
 
 class _RasterizeGaussians(torch.autograd.Function):
@@ -88,15 +112,15 @@ class _RasterizeGaussians(torch.autograd.Function):
                          "\nAn error occured in backward. Writing snapshot_bw.dump for debugging.\n") \
             if s.debug else None
         sink = _sh_factor_sink if (sh is not None and sh.numel() != 0) else None
+        if isinstance(sink, list):
+            sink = _ListSink(sink)
         try:
             (g_means2D, g_colors, g_opac, g_means3D, g_cov3D, g_sh, g_scales,
-             g_rot) = _C.rasterize_gaussians_backward(*call, sh_grad=sink is None)
+             g_rot) = _C.rasterize_gaussians_backward(*call, sh_grad=sink is None, factor_sink=sink, out=_take_out())
         except Exception:
             if dump:
                 dump()
             raise
-        if sink is not None:
-            sink.append((s.campos.detach().reshape(3), _C.sh_color_factors(geom, g_colors)))
         # order of forward's inputs; the settings tuple gets None (DGR __init__.py:143-153)
         return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None
 

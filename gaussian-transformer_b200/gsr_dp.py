@@ -40,7 +40,7 @@ class FlatGrads:
             for d in shp:
                 m *= int(d)
             self.slices[k] = (n, n + m)
-            n += m
+            n += (m + 3) & ~3  # every view starts 16-byte aligned (the kernels' 128-bit stores); padding stays 0
         self.flat = torch.zeros(n, dtype=torch.float32, device=device)
         self.views = {k: self.flat[a:b].view(self.shapes[k]) for k, (a, b) in self.slices.items()}
         self.bucket_elems = bucket_bytes // 4 if bucket_bytes else 0
@@ -54,7 +54,8 @@ class FlatGrads:
         for k, v in self.views.items():
             g = grads[k].reshape(v.shape)
             if self._first:
-                v.copy_(g)
+                if g.data_ptr() != v.data_ptr():  # grads_into(): the backward already wrote it in place
+                    v.copy_(g)
             else:
                 v.add_(g)
         self._first = False
@@ -90,6 +91,27 @@ def dp_step(render_backward: Callable[[int], Dict[str, torch.Tensor]], n_views: 
     return flat.views
 
 
+_C_NAMES = {"means3D": "means3D", "sh": "sh", "opacities": "opacity", "scales": "scales", "rotations": "rot"}
+
+
+class grads_into:
+    """Context manager: the first rasterizer backward inside writes its parameter gradients straight into the
+    views of `flat` (only while `flat` is still empty for this step), so that FlatGrads.add_ has nothing to copy."""
+
+    def __init__(self, flat: FlatGrads):
+        self.flat = flat
+
+    def __enter__(self):
+        import diff_gaussian_rasterization as dgr
+        self._dgr, self._prev = dgr, dgr._grad_out
+        dgr._grad_out = {_C_NAMES[k]: v for k, v in self.flat.views.items()} if self.flat._first else None
+        return self.flat
+
+    def __exit__(self, *exc):
+        self._dgr._grad_out = self._prev
+        return False
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # SH gradients by factor exchange.  For one view dL/dsh(i,k,c) = basis_k(dir_i) * f(i,c): a rank-1 product per
 # Gaussian (csrc/sh_exchange.cuh).  Instead of all-reducing 12*M B per Gaussian (192 B of the 236 B at M = 16),
@@ -100,44 +122,102 @@ SMALL_LEAVES = ("means3D", "opacities", "scales", "rotations")
 
 
 class capture_sh_factors:
-    """Context manager: rasterizer backward passes inside it skip dL/dsh and record (campos, factors) per view."""
+    """Context manager: rasterizer backward passes inside it skip dL/dsh and hand (campos, factors) of the view to
+    `sink` -- a FactorExchange, or by default a list that collects them."""
+
+    def __init__(self, sink=None):
+        self.sink = [] if sink is None else sink
 
     def __enter__(self):
         import diff_gaussian_rasterization as dgr
         self._dgr, self._prev = dgr, dgr._sh_factor_sink
-        dgr._sh_factor_sink = self.items = []
-        return self.items
+        dgr._sh_factor_sink = self.sink
+        return self.sink
 
     def __exit__(self, *exc):
         self._dgr._sh_factor_sink = self._prev
         return False
 
 
+class FactorExchange:
+    """All-gather of the batch's SH factors, one collective per view SLOT (the j-th view of every rank), launched
+    the moment this rank's j-th factors exist: the rasterizer calls emit() between its two backward stages, so
+    the transfer runs under preprocess_bwd and under the following views.  Buffers persist across steps.
+
+    Slot layout: fac_all[j, r] = factors of view j of rank r; ranks with fewer views contribute zeros (which add
+    nothing to the rebuilt gradient)."""
+
+    def __init__(self, per_rank: int, P: int, device, world: int, group=None):
+        f32 = dict(dtype=torch.float32, device=device)
+        self.per_rank, self.P, self.world, self.group = per_rank, P, world, group
+        self.fac = torch.zeros(per_rank, P, 3, **f32)
+        self.cam = torch.zeros(per_rank, 3, **f32)
+        self.fac_all = torch.zeros(per_rank, world, P, 3, **f32)
+        self.cam_all = torch.zeros(per_rank, world, 3, **f32)
+        self.active = world > 1 and dist.is_initialized()
+        self.nccl = self.active and dist.get_backend(group) == "nccl"
+        self.begin()
+
+    def begin(self):
+        self.n, self.works = 0, []
+
+    # -- the sink protocol of diff_gaussian_rasterization
+    def buffer(self, P, device):
+        if self.n >= self.per_rank:
+            raise ValueError("more local views than per_rank")
+        if P != self.P:
+            raise ValueError("FactorExchange was sized for %d Gaussians, got %d" % (self.P, P))
+        return self.fac[self.n]
+
+    def emit(self, campos, factors):
+        j = self.n
+        if j >= self.per_rank:
+            raise ValueError("more local views than per_rank")
+        if factors.data_ptr() != self.fac[j].data_ptr():
+            self.fac[j].copy_(factors.reshape(self.P, 3))
+        self.cam[j].copy_(campos.reshape(3))
+        self.n = j + 1
+        self._gather(j)
+
+    def _gather(self, j):
+        if not self.active:
+            self.fac_all[j, 0].copy_(self.fac[j])
+            self.cam_all[j, 0].copy_(self.cam[j])
+            return
+        for dst, src in ((self.fac_all[j], self.fac[j]), (self.cam_all[j], self.cam[j])):
+            if self.nccl:
+                w = dist.all_gather_into_tensor(dst, src, group=self.group, async_op=True)
+            else:
+                w = dist.all_gather(list(dst.unbind(0)), src, group=self.group, async_op=True)
+            self.works.append(w)
+
+    def pad(self):
+        """Launches the collectives of the slots this rank had no view for.  Every rank must issue its collectives
+        in the same order, so call this before any other collective that follows the views (finish() does)."""
+        while self.n < self.per_rank:
+            j = self.n
+            self.fac[j].zero_()
+            self.cam[j].zero_()
+            self.n = j + 1
+            self._gather(j)
+
+    def finish(self):
+        """Joins the collectives.  Returns campos (V,3) and factors (V,P,3), V = per_rank * world, identical on
+        every rank."""
+        self.pad()
+        for w in self.works:
+            w.wait()
+        self.works = []
+        return self.cam_all.view(-1, 3), self.fac_all.view(-1, self.P, 3)
+
+
 def gather_sh_factors(items, per_rank: int, P: int, device, world: int, group=None):
-    """items: this rank's [(campos (3,), factors (P,3))], at most `per_rank`; missing views are padded with zero
-    factors (they add nothing).  Returns campos (world*per_rank, 3) and factors (world*per_rank, P, 3), identical
-    on every rank."""
-    if len(items) > per_rank:
-        raise ValueError("more local views than per_rank")
-    cam = torch.zeros(per_rank, 3, dtype=torch.float32, device=device)
-    fac = torch.zeros(per_rank, P, 3, dtype=torch.float32, device=device) if len(items) < per_rank else \
-        torch.empty(per_rank, P, 3, dtype=torch.float32, device=device)
-    for j, (c, f) in enumerate(items):
-        cam[j].copy_(c.reshape(3))
-        fac[j].copy_(f.reshape(P, 3))
-    if world == 1 or not dist.is_initialized():
-        return cam, fac
-    cam_all = torch.empty(world * per_rank, 3, dtype=torch.float32, device=device)
-    fac_all = torch.empty(world * per_rank, P, 3, dtype=torch.float32, device=device)
-    if dist.get_backend(group) == "nccl":
-        w1 = dist.all_gather_into_tensor(fac_all, fac, group=group, async_op=True)
-        w2 = dist.all_gather_into_tensor(cam_all, cam, group=group, async_op=True)
-    else:
-        w1 = dist.all_gather(list(fac_all.view(world, per_rank, P, 3).unbind(0)), fac, group=group, async_op=True)
-        w2 = dist.all_gather(list(cam_all.view(world, per_rank, 3).unbind(0)), cam, group=group, async_op=True)
-    w1.wait()
-    w2.wait()
-    return cam_all, fac_all
+    """items: this rank's [(campos (3,), factors (P,3))], at most `per_rank`.  One-shot form of FactorExchange:
+    returns campos (world*per_rank, 3) and factors (world*per_rank, P, 3), identical on every rank."""
+    ex = FactorExchange(per_rank, P, device, world, group=group)
+    for c, f in items:
+        ex.emit(c, f)
+    return ex.finish()
 
 
 def _rebuild_cuda(means3D, campos, factors, degree, M):
@@ -145,24 +225,30 @@ def _rebuild_cuda(means3D, campos, factors, degree, M):
     return _C.sh_grad_from_factors(means3D, campos, factors, degree, M)
 
 
-def dp_step_factored(render_backward: Callable[[int], Dict[str, torch.Tensor]], n_views: int, flat_small: FlatGrads,
+def dp_step_factored(render_backward: Callable[..., Dict[str, torch.Tensor]], n_views: int, flat_small: FlatGrads,
                      rank: int, world: int, means3D: torch.Tensor, degree: int, M: int, rebuild=_rebuild_cuda,
-                     group=None) -> Dict[str, torch.Tensor]:
-    """Like dp_step, but `render_backward(v)` returns the SMALL_LEAVES gradients plus "sh_factor": (campos,
-    factors) of the view; the summed dL/dsh is rebuilt from the all-gathered factors.  Returns the reduced
-    gradients of all five parameters."""
+                     group=None, exchange: "FactorExchange" = None) -> Dict[str, torch.Tensor]:
+    """Like dp_step, but `render_backward(v, exchange)` returns only the SMALL_LEAVES gradients and hands the
+    view's SH factors to `exchange` (run the rasterizer backward inside `capture_sh_factors(exchange)`, or call
+    `exchange.emit(campos, factors)`); the summed dL/dsh is rebuilt from the all-gathered factors while the
+    all-reduce of the small gradients is in flight.  Returns the reduced gradients of all five parameters."""
     per_rank = (n_views + world - 1) // world
-    items = []
+    P = means3D.shape[0]
+    ex = exchange if exchange is not None else FactorExchange(per_rank, P, means3D.device, world, group=group)
+    if ex.per_rank != per_rank or ex.P != P or ex.world != world:
+        raise ValueError("exchange was built for another batch shape")
+    ex.begin()
     flat_small.zero_()
     for v in shard_views(n_views, rank, world):
-        g = render_backward(v)
-        flat_small.add_(g)
-        items.append(g["sh_factor"])
+        seen = ex.n
+        flat_small.add_(render_backward(v, ex))
+        if ex.n != seen + 1:
+            raise RuntimeError("render_backward must hand exactly one view's SH factors to the exchange")
+    ex.pad()  # same collective order on every rank: all slots first, then the all-reduce
     works = flat_small.all_reduce(group=group, async_op=True)
-    P = means3D.shape[0]
-    cam_all, fac_all = gather_sh_factors(items, per_rank, P, means3D.device, world, group=group)
-    for w in works:
-        w.wait()
+    cam_all, fac_all = ex.finish()
     out = dict(flat_small.views)
     out["sh"] = rebuild(means3D, cam_all, fac_all, degree, M)
+    for w in works:
+        w.wait()
     return out

@@ -137,6 +137,20 @@ GSR_API int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void*
                  float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
                  float* dL_dconic, void* bwd_scratch, void* stream);
 
+/* The same backward in its two stages, for callers that start work between them (the data-parallel exchange below
+ * launches the all-gather of a view's SH factors while stage 2 runs):
+ *   gsr_backward_blend     BACKWARD::render (backward.cu:399-557): per-pixel gradients -> per-Gaussian accumulators
+ *                          in bwd_scratch (zeroed here);
+ *   gsr_backward_geometry  computeCov2DCUDA + preprocessCUDA (backward.cu:144-396): accumulators -> the outputs of
+ *                          gsr_backward, same meaning and NULL rules.
+ * gsr_backward(...) == gsr_backward_blend(...) followed by gsr_backward_geometry(...) with the same arguments. */
+GSR_API int gsr_backward_blend(const gsr_inputs* in, const void* geom, const void* binning, const void* image,
+                               int64_t R, const float* dL_dpix, void* bwd_scratch, void* stream);
+GSR_API int gsr_backward_geometry(const gsr_inputs* in, const int32_t* radii, const void* geom,
+                                  float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dsh, float* dL_dcolors,
+                                  float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                                  float* dL_dconic, void* bwd_scratch, void* stream);
+
 /* Data-parallel SH gradient exchange (no reference counterpart: the reference is single-GPU; this serves the
  * view-sharded path of SURVEY.md section 8e).  For one view, dL/dsh(i,k,c) = basis_k(dir_i) * f(i,c) with
  * f = dL/dcolor whose forward-clamped channels are zeroed (DGR/cuda_rasterizer/backward.cu:20-139), a rank-1
@@ -144,11 +158,14 @@ GSR_API int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void*
  * Gaussian, call gsr_backward with dL_dsh = NULL, and rebuild the sum over all views locally:
  *   gsr_sh_color_factors:      factors float[P*3] out, from the dL_dcolors of gsr_backward and the geom buffer of
  *                              the same forward;
+ *   gsr_backward_sh_factors:   the same factors read from bwd_scratch right after gsr_backward_blend;
  *   gsr_sh_grad_from_factors:  dL_dsh float[P*M*3] (+)= sum_v basis(normalize(means3D - campos[v])) (x) factors[v];
  *                              campos float[V*3] and factors float[V*P*3] are DEVICE arrays; accumulate = 0
  *                              overwrites (every element written), 1 adds to the existing content. */
 GSR_API int gsr_sh_color_factors(int32_t P, const void* geom, const float* dL_dcolors, float* factors,
                                  void* stream);
+GSR_API int gsr_backward_sh_factors(int32_t P, const void* geom, const void* bwd_scratch, float* factors,
+                                    void* stream);
 GSR_API int gsr_sh_grad_from_factors(int32_t P, int32_t D, int32_t M, int32_t V, const float* means3D,
                                      const float* campos, const float* factors, float* dL_dsh,
                                      int32_t accumulate, void* stream);

@@ -53,15 +53,14 @@ def _rebuild_numpy(means3D, campos, factors, degree, M):
     return torch.from_numpy(out.astype(np.float32))
 
 
-def _view_grads_factored(orc, v):
-    """Small-parameter gradients + the view's SH factor.  The factor (masked dL/dcolor) is recovered from the
-    oracle's dL/dsh row 0, which is SH_C0 * factor (backward.cu:44)."""
+def _view_grads_factored(orc, v, exchange):
+    """Small-parameter gradients; the view's SH factor goes to the exchange.  The factor (masked dL/dcolor) is
+    recovered from the oracle's dL/dsh row 0, which is SH_C0 * factor (backward.cu:44)."""
     yaw = -15.0 + 30.0 * v / (N_VIEWS - 1)
     sc = S.scene_S(P, W, H, seed=11, M=M, sh_degree=DEG, yaw_deg=yaw)
     g = _view_grads(orc, v)
-    out = {k: g[k] for k in gsr_dp.SMALL_LEAVES}
-    out["sh_factor"] = (torch.from_numpy(sc["campos"].copy()), g["sh"][:, 0, :] / S.SH_C0)
-    return out
+    exchange.emit(torch.from_numpy(sc["campos"].copy()), g["sh"][:, 0, :] / S.SH_C0)
+    return {k: g[k] for k in gsr_dp.SMALL_LEAVES}
 
 
 def _worker_factored(rank, world, port, out_dir):
@@ -73,8 +72,10 @@ def _worker_factored(rank, world, port, out_dir):
         shapes = {k: v for k, v in _shapes().items() if k in gsr_dp.SMALL_LEAVES}
         flat = gsr_dp.FlatGrads(shapes, "cpu")
         means = torch.from_numpy(S.scene_S(P, W, H, seed=11, M=M, sh_degree=DEG)["means3D"])
-        out = gsr_dp.dp_step_factored(lambda v: _view_grads_factored(orc, v), N_VIEWS, flat, rank, world, means, DEG,
-                                      M, rebuild=_rebuild_numpy)
+        ex = gsr_dp.FactorExchange((N_VIEWS + world - 1) // world, P, "cpu", world)
+        for step in range(2):  # the exchange buffers persist: the second step must not see the first one's
+            out = gsr_dp.dp_step_factored(lambda v, e: _view_grads_factored(orc, v, e), N_VIEWS, flat, rank, world,
+                                          means, DEG, M, rebuild=_rebuild_numpy, exchange=ex)
         np.save(os.path.join(out_dir, f"fact_{rank}.npy"),
                 torch.cat([out[k].reshape(-1) for k in gsr_dp.LEAVES]).numpy())
     finally:

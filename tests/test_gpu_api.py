@@ -1,5 +1,7 @@
 """GPU tests of the Python surface (GaussianRasterizer / rasterize_gaussians / markVisible): every argument
 combination of DGR/diff_gaussian_rasterization/__init__.py:187-220, autograd wiring, edge cases."""
+import contextlib
+
 import numpy as np
 import pytest
 import torch
@@ -78,6 +80,43 @@ def test_sh_factor_exchange_matches_plain_sh_gradient():
     # generic (non-staged) variant: M = 4, degree 1
     r4 = _C.sh_grad_from_factors(means, cam, fac, 1, 4)
     assert rel_err(np_(r4), np_(_C.sh_grad_from_factors(means, cam, fac, 1, 16)[:, :4])) <= 1e-6
+
+
+def test_factor_exchange_sink_and_staged_backward():
+    """A FactorExchange as the sink: factors land in its buffer between the two backward stages and equal both
+    the list sink's and gsr_sh_color_factors(dL_dcolors); the staged backward equals the one-call backward."""
+    import gsr_dp
+    from diff_gaussian_rasterization import _C
+    sc = S.scene_S(3000, 320, 208, seed=6, M=16, sh_degree=3, yaw_deg=4.0)
+    d = to_device(sc)
+    dpix = torch.from_numpy(S.upstream_grad(sc["W"], sc["H"], 6)).cuda()
+    got = []
+    for sink in (None, [], gsr_dp.FactorExchange(1, 3000, d["means3D"].device, 1)):
+        m3, sh, op, scl, rot = (_leaf(d[k]) for k in ("means3D", "sh", "opacities", "scales", "rotations"))
+        with gsr_dp.capture_sh_factors(sink) if sink is not None else contextlib.nullcontext():
+            color, _ = _module(d)(means3D=m3, means2D=torch.zeros_like(m3), opacities=op, shs=sh, scales=scl,
+                                  rotations=rot)
+            (color * dpix).sum().backward()
+        got.append((m3.grad, op.grad, scl.grad, rot.grad))
+    for k in (1, 2):
+        for a, b in zip(got[0], got[k]):
+            assert rel_err(np_(b), np_(a)) <= 1e-3
+    ex = sink
+    cam, fac = ex.finish()
+    assert cam.shape == (1, 3) and fac.shape == (1, 3000, 3)
+    np.testing.assert_array_equal(np_(cam[0]), sc["campos"].reshape(3))
+    # list sink of the second run: same factors up to the order of the blend atomics
+    # (both come from the accumulators of their own backward)
+    e = torch.Tensor([])
+    R, c, radii, geom, binning, img = _C.rasterize_gaussians(
+        d["bg"], d["means3D"], e, d["opacities"], d["scales"], d["rotations"], 1.0, e, d["viewmatrix"],
+        d["projmatrix"], d["tanfovx"], d["tanfovy"], sc["H"], sc["W"], d["sh"], 3, d["campos"], False, False)
+    g = _C.rasterize_gaussians_backward(d["bg"], d["means3D"], radii, e, d["scales"], d["rotations"], 1.0, e,
+                                        d["viewmatrix"], d["projmatrix"], d["tanfovx"], d["tanfovy"], dpix, d["sh"],
+                                        3, d["campos"], geom, R, binning, img, False)
+    want = _C.sh_color_factors(geom, g[1])
+    assert float(want.abs().max()) > 0
+    assert rel_err(np_(fac[0]), np_(want)) <= 1e-3
 
 
 def test_colors_and_cov_paths():
