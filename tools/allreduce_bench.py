@@ -1,4 +1,6 @@
-"""Dev tool (torchrun): time the per-step gradient exchange alone -- NCCL all-reduce of the flat 236 B/Gaussian buffer."""
+"""Dev tool (torchrun): time the per-step gradient exchange collectives alone -- NCCL all-reduce of the flat
+236 B/Gaussian buffer (plain exchange), of the 44 B/Gaussian small-leaf buffer and the all-gather of 12 B/Gaussian
+SH factors (factored exchange).  Run under different NCCL_ALGO / NCCL_PROTO to see what NCCL's tuner leaves behind."""
 import os
 import sys
 
@@ -9,11 +11,12 @@ rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os
 torch.cuda.set_device(lr)
 dist.init_process_group("nccl", device_id=torch.device("cuda", lr))
 P = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
-n = P * 59
-x = torch.randn(n, device="cuda")
-src = torch.randn(n, device="cuda")
-for name, fn in (("all_reduce %d MB" % (n * 4 // 10**6), lambda: dist.all_reduce(x)),
-                 ("copy into flat", lambda: x.copy_(src))):
+big, small = torch.randn(P * 59, device="cuda"), torch.randn(P * 11, device="cuda")
+fac, fac_all = torch.randn(P * 3, device="cuda"), torch.empty(world * P * 3, device="cuda")
+tag = "ALGO=%s PROTO=%s" % (os.environ.get("NCCL_ALGO", "-"), os.environ.get("NCCL_PROTO", "-"))
+for name, nbytes, fn in (("all_reduce 236 B/G", big.numel() * 4, lambda: dist.all_reduce(big)),
+                         ("all_reduce  44 B/G", small.numel() * 4, lambda: dist.all_reduce(small)),
+                         ("all_gather  12 B/G", fac_all.numel() * 4, lambda: dist.all_gather_into_tensor(fac_all, fac))):
     for _ in range(5):
         fn()
     torch.cuda.synchronize()
@@ -28,6 +31,7 @@ for name, fn in (("all_reduce %d MB" % (n * 4 // 10**6), lambda: dist.all_reduce
     t = torch.tensor([ms], device="cuda")
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     if rank == 0:
-        print(f"{name}: {float(t):.3f} ms  (world {world}; algbw {n * 4 / float(t) / 1e6:.0f} GB/s)")
+        print(f"[{tag}] {name}: {float(t) * 1e3:.0f} us  (world {world}; {nbytes / 1e6:.0f} MB, "
+              f"{nbytes / float(t) / 1e6:.0f} GB/s)", flush=True)
 dist.barrier()
 dist.destroy_process_group()
