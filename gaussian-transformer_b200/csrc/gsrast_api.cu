@@ -16,6 +16,7 @@
 #include "depth_sort.cuh"
 #include "knn.cuh"
 #include "loss.cuh"
+#include "adam.cuh"
 #include "preprocess_bwd.cuh"
 #include "preprocess_fwd.cuh"
 #include "render_bwd.cuh"
@@ -564,6 +565,44 @@ int gsr_l1_ssim_loss(int32_t C, int32_t H, int32_t W, const float* img, const fl
                                                     (float)(lambda_dssim / n), dL_dimg);
     GSR_STAGE("loss_pass2", 0, stream);
   }
+  return GSR_OK;
+}
+
+// ---- fused multi-group Adam step
+int gsr_adam_step(int32_t n_groups, const gsr_adam_group* groups, double beta1, double beta2, double eps,
+                  void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n_groups < 0 || n_groups > ADAM_MAX_GROUPS) return fail(GSR_ERR_INVALID, "gsr_adam_step: 0..8 groups per call");
+  if (n_groups > 0 && !groups) return fail(GSR_ERR_INVALID, "gsr_adam_step: NULL groups");
+  AdamArgs a;
+  memset(&a, 0, sizeof(a));
+  long long blocks = 0;
+  int k = 0;
+  for (int i = 0; i < n_groups; i++) {
+    const gsr_adam_group& s = groups[i];
+    if (s.n < 0 || s.step < 1) return fail(GSR_ERR_INVALID, "gsr_adam_step: n < 0 or step < 1");
+    if (s.n == 0) continue;
+    if (!s.param || !s.grad || !s.exp_avg || !s.exp_avg_sq) return fail(GSR_ERR_INVALID, "gsr_adam_step: NULL array");
+    AdamGroup& g = a.grp[k++];
+    g.p = s.param; g.g = s.grad; g.m = s.exp_avg; g.v = s.exp_avg_sq; g.n = s.n;
+    // torch/optim/adam.py: bias_correction = 1 - beta ** step, step_size = lr / bias_correction1,
+    // bias_correction2_sqrt = bias_correction2 ** 0.5 -- Python doubles, cast to float32 at the tensor op
+    const double bc1 = 1.0 - pow(beta1, (double)s.step), bc2 = 1.0 - pow(beta2, (double)s.step);
+    g.neg_step_size = (float)(-(s.lr / bc1));
+    g.bc2_sqrt = (float)sqrt(bc2);
+    g.first_block = (int)blocks;
+    g.vec = aligned16(s.param) && aligned16(s.grad) && aligned16(s.exp_avg) && aligned16(s.exp_avg_sq);
+    blocks += (s.n + ADAM_CHUNK - 1) / ADAM_CHUNK;
+    if (blocks > 0x7fffffffLL) return fail(GSR_ERR_INVALID, "gsr_adam_step: too many elements for one launch");
+  }
+  if (blocks == 0) return GSR_OK;
+  a.n_groups = k;
+  a.w1 = (float)(1.0 - beta1);  // Python doubles in torch, rounded to float32 at the tensor op
+  a.beta2 = (float)beta2;
+  a.w2 = (float)(1.0 - beta2);
+  a.eps = (float)eps;
+  adam_step_kernel<<<(unsigned)blocks, ADAM_THREADS, 0, stream>>>(a);
+  GSR_STAGE("adam_step", 0, stream);
   return GSR_OK;
 }
 

@@ -37,6 +37,7 @@ EXPORTS = (
     "gsr_sh_color_factors", "gsr_sh_grad_from_factors", "gsr_knn_scratch_bytes", "gsr_knn_dist2",
     "gsr_loss_scratch_bytes", "gsr_l1_ssim_loss",
     "gsr_backward_blend", "gsr_backward_geometry", "gsr_backward_sh_factors",
+    "gsr_adam_step",
 )
 STAGES = ("preprocess_fwd", "depth_sort", "bin_count", "bin_scatter", "render_fwd", "render_bwd", "preprocess_bwd")
 
@@ -60,6 +61,7 @@ def load(path=LIB_PATH):
     lib.gsr_backward_blend.argtypes = [inp, vp, vp, vp, i64, vp, vp, vp]
     lib.gsr_backward_geometry.argtypes = [inp, vp, vp] + [vp] * 9 + [vp, vp]
     lib.gsr_backward_sh_factors.argtypes = [i32, vp, vp, vp, vp]
+    lib.gsr_adam_step.argtypes = [i32, vp, ctypes.c_double, ctypes.c_double, ctypes.c_double, vp]
     lib.gsr_mark_visible.argtypes = [i32, vp, vp, vp, vp, vp]
     lib.gsr_loss_scratch_bytes.argtypes = [i32, i32, i32, szp]
     lib.gsr_l1_ssim_loss.argtypes = [i32, i32, i32, vp, vp, ctypes.c_float, vp, vp, vp, vp]

@@ -191,6 +191,24 @@ GSR_API int gsr_loss_scratch_bytes(int32_t C, int32_t H, int32_t W, size_t* byte
 GSR_API int gsr_l1_ssim_loss(int32_t C, int32_t H, int32_t W, const float* img, const float* gt,
                              float lambda_dssim, float* out3, float* dL_dimg, void* scratch, void* stream);
 
+/* Fused Adam step over up to 8 parameter groups in ONE launch: replaces the torch.optim.Adam(l, lr=0.0, eps=1e-15)
+ * step of scene/gaussian_model.py:149-167 / train.py:126-128 (betas (0.9, 0.999) by default, no weight decay, no
+ * amsgrad; torch/optim/adam.py op order, bias corrections in double on the host).  Arrays are device float32 and
+ * updated in place; `step` is the 1-based step count of that group's state AFTER this update; lr is read per call
+ * (the reference reschedules the xyz group's lr every iteration, gaussian_model.py:169-175). */
+typedef struct gsr_adam_group {
+  float* param;
+  const float* grad;
+  float* exp_avg;
+  float* exp_avg_sq;
+  int64_t n;
+  int64_t step;
+  double lr;
+} gsr_adam_group;
+/* beta1, beta2, eps, lr are doubles: torch forms 1 - beta and lr / (1 - beta1^t) in double before rounding to float32 */
+GSR_API int gsr_adam_step(int32_t n_groups, const gsr_adam_group* groups, double beta1, double beta2, double eps,
+                          void* stream);
+
 /* present[i] = (view-space z > 0.2).  Replaces Rasterizer::markVisible /
  * checkFrustum (DGR/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153). */
 GSR_API int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,

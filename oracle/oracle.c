@@ -900,3 +900,21 @@ void orc_l1_ssim(int C, int H, int W, const float* img, const float* gt, double 
   }
   free(maps);
 }
+
+/* ---- Adam step: torch.optim.Adam as scene/gaussian_model.py:163 configures it
+ * (no weight decay, no amsgrad), per element in float32 with torch's op order (torch/optim/adam.py:
+ * lerp, mul + addcmul, sqrt / bias_correction2_sqrt + eps, addcdiv); bias corrections in double.  Pinned against
+ * torch.optim.Adam itself in tests/test_cpu_adam.py.  step = 1-based count after this update. */
+void orc_adam_step(long n, float* p, const float* g, float* m, float* v, long step, double lr, double beta1,
+                   double beta2, double eps) {
+  const double bc1 = 1.0 - pow(beta1, (double)step), bc2 = 1.0 - pow(beta2, (double)step);
+  const float neg_step = (float)(-(lr / bc1)), bc2s = (float)sqrt(bc2);
+  const float w1 = (float)(1.0 - beta1), b2 = (float)beta2, w2 = (float)(1.0 - beta2), e = (float)eps;
+  for (long i = 0; i < n; i++) {
+    m[i] = fmaf(w1, g[i] - m[i], m[i]);
+    const float t = w2 * g[i];
+    v[i] = fmaf(t, g[i], v[i] * b2);
+    const float denom = sqrtf(v[i]) / bc2s + e;
+    p[i] = fmaf(neg_step, m[i] / denom, p[i]);
+  }
+}

@@ -153,6 +153,15 @@ class Oracle:
         self.lib.orc_l1_ssim(C, H, W, _p(img), _p(gt), float(lambda_dssim), _p(out3), _p(g))
         return out3, g
 
+    def adam_step(self, p, g, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-15):
+        """In-place Adam update of float32 numpy arrays p, m, v (oracle.c orc_adam_step)."""
+        for a in (p, g, m, v):
+            assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
+        self.lib.orc_adam_step.argtypes = [_c.c_long, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_void_p, _c.c_long,
+                                           _c.c_double, _c.c_double, _c.c_double, _c.c_double]
+        self.lib.orc_adam_step.restype = None
+        self.lib.orc_adam_step(p.size, _p(p), _p(g), _p(m), _p(v), int(step), lr, beta1, beta2, eps)
+
     def knn3(self, points):
         """(P,) mean squared distance to the 3 nearest neighbours, brute force (oracle.c orc_knn3)."""
         pts = _np_f(points)
