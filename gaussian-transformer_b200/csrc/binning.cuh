@@ -73,9 +73,11 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_pass_kernel(int P, const u
                                                                   BinPlan plan, uint32_t* __restrict__ matrix,
                                                                   const uint2* __restrict__ ranges,
                                                                   uint32_t* __restrict__ point_list,
-                                                                  const uint2* __restrict__ rects) {
+                                                                  const uint2* __restrict__ rects,
+                                                                  const uint32_t* __restrict__ guard, uint32_t cap) {
   extern __shared__ uint32_t s_tab[];
   __shared__ uint4 s_desc[BIN_WARPS][32];  // per warp: the step's live Gaussians, compacted in order
+  if (guard != nullptr && (guard[CTRL_R_HI] != 0u || guard[CTRL_R_LO] > cap)) return;  // see render_fwd_kernel
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int task = blockIdx.x * BIN_WARPS + w;
   if (task >= plan.n_chunks * plan.n_bands) return;

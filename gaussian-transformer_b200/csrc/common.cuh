@@ -77,7 +77,7 @@ struct BwdView {
 };
 
 // ctrl[] slots
-enum { CTRL_FLAGS = 0, CTRL_R_LO = 4, CTRL_R_HI = 5, CTRL_WORDS = 64 };
+enum { CTRL_R_LO = 4, CTRL_R_HI = 5, CTRL_FLAGS = 6, CTRL_WORDS = 64 };  // words 4..7 go to the host in one copy
 
 #ifndef GSR_SORT_ROUNDS
 #define GSR_SORT_ROUNDS 4

@@ -285,7 +285,7 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
     GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
              "bin_pass smem attribute");
     bin_pass_kernel<false><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
-        in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, nullptr, nullptr);
+        in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, nullptr, nullptr, nullptr, 0u);
   }
   GSR_STAGE("bin_count", in->debug, stream);
   column_scan_kernel<<<((int)T + 31) / 32, 1024, 0, stream>>>(im.matrix, plan.n_chunks, (int)T, im.tile_count);
@@ -294,14 +294,18 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   GSR_STAGE("tile_scan", in->debug, stream);
   }
   // ctrl[CTRL_R_LO..HI] -> host_result[0] (little endian int64), flags -> [1]
-  GSR_CUDA(cudaMemcpyAsync(&host_result[0], im.ctrl + CTRL_R_LO, 8, cudaMemcpyDeviceToHost, stream), "copy R");
-  GSR_CUDA(cudaMemcpyAsync(&host_result[1], im.ctrl + CTRL_FLAGS, 4, cudaMemcpyDeviceToHost, stream), "copy flags");
+  static_assert(CTRL_R_HI == CTRL_R_LO + 1 && CTRL_FLAGS == CTRL_R_LO + 2, "ctrl words 4..7 = R, flags, 0");
+  GSR_CUDA(cudaMemcpyAsync(host_result, im.ctrl + CTRL_R_LO, 16, cudaMemcpyDeviceToHost, stream), "copy R, flags");
   return GSR_OK;
 }
 
-int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void* image, int64_t R,
-                     float* out_color, void* stream_) {
-  cudaStream_t stream = (cudaStream_t)stream_;
+}  // extern "C"
+
+namespace {
+// Phase 2 of the forward.  speculative: R is an upper bound (the capacity of `binning` in list entries) and the
+// kernels check the device-side num_rendered against it themselves.
+int forward_post_impl(const gsr_inputs* in, const void* geom, void* binning, void* image, int64_t R, bool speculative,
+                      float* out_color, cudaStream_t stream) {
   if (int rc = check_inputs(in)) return rc;
   if (!out_color) return fail(GSR_ERR_INVALID, "out_color is NULL");
   if (R < 0) return fail(GSR_ERR_INVALID, "R < 0");
@@ -318,6 +322,8 @@ int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void
   GeomView g = geom_view(const_cast<void*>(geom), (size_t)in->P);
   ImageView im = image_view(image, N, T);
   BinView b = bin_view(binning, (size_t)R);
+  const uint32_t* guard = speculative ? im.ctrl : nullptr;
+  const uint32_t cap = (uint32_t)R;
   if (R > 0) {
     ScopedStage prof_(GSR_STAGE_BIN_SCATTER, stream);
     const BinPlan plan = make_bin_plan(in->P, cam.gx, cam.gy);
@@ -329,15 +335,55 @@ int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void
                "bin_pass smem attribute");
       bin_pass_kernel<true><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
           in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list,
-          bin_parallel(T, plan) ? g.rects : nullptr);
+          bin_parallel(T, plan) ? g.rects : nullptr, guard, cap);
       GSR_STAGE("bin_scatter", in->debug, stream);
     }
   }
   ScopedStage prof_(GSR_STAGE_RENDER_FWD, stream);
   dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
   render_fwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, g.g0, g.g1, g.g2,
-                                                in->colors_precomp, in->bg, im.final_T, im.n_contrib, out_color);
+                                                in->colors_precomp, in->bg, im.final_T, im.n_contrib, out_color,
+                                                guard, cap);
   GSR_STAGE("render_fwd", in->debug, stream);
+  return GSR_OK;
+}
+
+// one event per host thread for gsr_forward's "R is on the host" wait
+cudaEvent_t forward_event() {
+  thread_local cudaEvent_t ev = nullptr;
+  thread_local int ev_dev = -1;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (ev == nullptr || ev_dev != dev) {
+    if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+    ev_dev = dev;
+  }
+  return ev;
+}
+}  // namespace
+
+extern "C" {
+
+int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning, void* image, int64_t R,
+                     float* out_color, void* stream_) {
+  return forward_post_impl(in, geom, binning, image, R, false, out_color, (cudaStream_t)stream_);
+}
+
+int gsr_forward(const gsr_inputs* in, void* geom, void* binning, int64_t capacity_R, void* image, int32_t* radii,
+                int64_t* host_result, float* out_color, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (capacity_R < 0) return fail(GSR_ERR_INVALID, "gsr_forward: capacity_R < 0");
+  if (capacity_R > 0x7fffffffLL) capacity_R = 0x7fffffffLL;
+  if (int rc = gsr_forward_pre(in, geom, image, radii, host_result, stream_)) return rc;
+  if (in->P == 0) return forward_post_impl(in, geom, binning, image, 0, false, out_color, stream);
+  cudaEvent_t ev = forward_event();
+  if (!ev) return fail(GSR_ERR_CUDA, "gsr_forward: cudaEventCreate failed");
+  GSR_CUDA(cudaEventRecord(ev, stream), "record R event");
+  if (capacity_R > 0 && binning) {
+    // phase 2 goes out BEFORE the host knows num_rendered: no GPU idle time across the round trip
+    if (int rc = forward_post_impl(in, geom, binning, image, capacity_R, true, out_color, stream)) return rc;
+  }
+  GSR_CUDA(cudaEventSynchronize(ev), "wait for num_rendered");
   return GSR_OK;
 }
 

@@ -62,6 +62,9 @@ def _check_means(means3D):
         raise RuntimeError("gsrast: means3D must be a CUDA tensor (there is no CPU path)")
 
 
+_r_hint = {}  # device index -> largest num_rendered seen (sizes the speculative binning buffer)
+
+
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
                         prefiltered, debug):
@@ -86,18 +89,26 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         out_color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
         host = _host_result()
         stream = torch.cuda.current_stream(dev)
-        _lib.check(_lib.lib.gsr_forward_pre(ctypes.byref(args), geom.data_ptr(), image.data_ptr(), radii.data_ptr(),
-                                            host.data_ptr(), stream.cuda_stream))
-        stream.synchronize()  # the one host round trip (rasterizer_impl.cu:281)
+        # Phase 2 is launched speculatively against a binning buffer sized from the largest num_rendered seen so far
+        # on this device (+25 %), so the GPU does not idle during the one host round trip (rasterizer_impl.cu:281);
+        # a miss (first call, or a much denser view) falls back to allocate-then-launch.
+        hint = _r_hint.get(dev.index, 0)
+        cap = min(hint + hint // 4 + 65536, 0x7FFFFFFF) if hint > 0 else 0
+        binning = torch.empty(_lib.scratch_bytes(P, cap, W, H)[1] if cap > 0 else 0, **u8)
+        _lib.check(_lib.lib.gsr_forward(ctypes.byref(args), geom.data_ptr(), _ptr(binning) if cap > 0 else 0, cap,
+                                        image.data_ptr(), radii.data_ptr(), host.data_ptr(), out_color.data_ptr(),
+                                        stream.cuda_stream))
         R, flags = int(host[0]), int(host[1])
         if flags & 1:
             raise RuntimeError("gsrast: point is filtered although prefiltered is set. This shouldn't happen!")
         if R > 0x7FFFFFFF:
             raise RuntimeError(f"gsrast: num_rendered = {R} does not fit a 32-bit int")
-        _, bb, _, _ = _lib.scratch_bytes(P, R, W, H)
-        binning = torch.empty(bb if R > 0 else 0, **u8)
-        _lib.check(_lib.lib.gsr_forward_post(ctypes.byref(args), geom.data_ptr(), _ptr(binning) if R > 0 else 0,
-                                             image.data_ptr(), R, out_color.data_ptr(), stream.cuda_stream))
+        _r_hint[dev.index] = max(hint, R)
+        if R > cap or cap == 0:
+            _, bb, _, _ = _lib.scratch_bytes(P, R, W, H)
+            binning = torch.empty(bb if R > 0 else 0, **u8)
+            _lib.check(_lib.lib.gsr_forward_post(ctypes.byref(args), geom.data_ptr(), _ptr(binning) if R > 0 else 0,
+                                                 image.data_ptr(), R, out_color.data_ptr(), stream.cuda_stream))
     return R, out_color, radii, geom, binning, image
 
 

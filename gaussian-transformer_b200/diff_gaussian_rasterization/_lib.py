@@ -37,7 +37,7 @@ EXPORTS = (
     "gsr_sh_color_factors", "gsr_sh_grad_from_factors", "gsr_knn_scratch_bytes", "gsr_knn_dist2",
     "gsr_loss_scratch_bytes", "gsr_l1_ssim_loss",
     "gsr_backward_blend", "gsr_backward_geometry", "gsr_backward_sh_factors",
-    "gsr_adam_step",
+    "gsr_adam_step", "gsr_forward",
 )
 STAGES = ("preprocess_fwd", "depth_sort", "bin_count", "bin_scatter", "render_fwd", "render_bwd", "preprocess_bwd")
 
@@ -57,6 +57,7 @@ def load(path=LIB_PATH):
     lib.gsr_scratch_bytes.argtypes = [i32, i64, i32, i32, szp, szp, szp, szp]
     lib.gsr_forward_pre.argtypes = [inp, vp, vp, vp, vp, vp]
     lib.gsr_forward_post.argtypes = [inp, vp, vp, vp, i64, vp, vp]
+    lib.gsr_forward.argtypes = [inp, vp, vp, i64, vp, vp, vp, vp, vp]
     lib.gsr_backward.argtypes = [inp, vp, vp, vp, vp, i64, vp] + [vp] * 9 + [vp, vp]
     lib.gsr_backward_blend.argtypes = [inp, vp, vp, vp, i64, vp, vp, vp]
     lib.gsr_backward_geometry.argtypes = [inp, vp, vp] + [vp] * 9 + [vp, vp]

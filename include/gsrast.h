@@ -116,6 +116,16 @@ GSR_API int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32
 GSR_API int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binning,
                      void* image, int64_t R, float* out_color, void* stream);
 
+/* Both phases in one call, without GPU idle time across the num_rendered round trip: phase 2 is launched
+ * speculatively against a binning buffer sized for capacity_R list entries (gsr_scratch_bytes(P, capacity_R, ...));
+ * its kernels compare the device-side num_rendered with capacity_R and do nothing when it does not fit.  Returns
+ * once host_result is valid (the GPU may still be rendering).  The caller checks host_result[0]:
+ *   <= capacity_R : done, out_color / image / binning are (being) written on `stream`;
+ *   >  capacity_R : allocate gsr_scratch_bytes(P, R, ...) and call gsr_forward_post as usual.
+ * capacity_R = 0 (or binning = NULL) runs phase 1 only. */
+GSR_API int gsr_forward(const gsr_inputs* in, void* geom, void* binning, int64_t capacity_R, void* image,
+                        int32_t* radii, int64_t* host_result, float* out_color, void* stream);
+
 /* Backward.  Replaces CudaRasterizer::Rasterizer::backward
  * (DGR/cuda_rasterizer/rasterizer_impl.cu:340-434; BACKWARD::render
  * backward.cu:399-557, computeCov2DCUDA :144-274, preprocessCUDA :346-396) and

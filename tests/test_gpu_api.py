@@ -119,6 +119,36 @@ def test_factor_exchange_sink_and_staged_backward():
     assert rel_err(np_(fac[0]), np_(want)) <= 1e-3
 
 
+def test_speculative_forward_hit_miss_and_overflow_guard():
+    """gsr_forward launches phase 2 before num_rendered reaches the host, against a buffer sized from a hint: a
+    hit, a miss (hint far too small: the device-side guard must keep the kernels from touching the short buffer)
+    and the no-hint first call all return the same bits."""
+    from diff_gaussian_rasterization import _C
+    sc = S.scene_S(20000, 640, 360, seed=8, M=16, sh_degree=3)
+    d = to_device(sc)
+    e = torch.Tensor([])
+    dev = d["means3D"].device.index
+
+    def fwd():
+        return _C.rasterize_gaussians(d["bg"], d["means3D"], e, d["opacities"], d["scales"], d["rotations"], 1.0, e,
+                                      d["viewmatrix"], d["projmatrix"], d["tanfovx"], d["tanfovy"], sc["H"], sc["W"],
+                                      d["sh"], 3, d["campos"], False, False)
+    _C._r_hint.pop(dev, None)
+    R0, c0, radii0, _, b0, i0 = fwd()                  # no hint: phase 1, round trip, phase 2
+    assert R0 > 1000 and _C._r_hint[dev] == R0
+    R1, c1, radii1, _, b1, i1 = fwd()                  # hit: speculative launch
+    assert b1.numel() > b0.numel()                     # over-allocated by the 25 % margin
+    _C._r_hint[dev] = 10                               # miss: capacity of ~65k entries < R
+    if R0 <= 10 + 2 + 65536:
+        pytest.skip("scene too sparse to overflow the minimum capacity")
+    R2, c2, radii2, _, b2, i2 = fwd()
+    assert R0 == R1 == R2
+    for c, r, b, i in ((c1, radii1, b1, i1), (c2, radii2, b2, i2)):
+        assert torch.equal(c, c0) and torch.equal(r, radii0) and torch.equal(i, i0)
+        assert torch.equal(b[:4 * R0], b0[:4 * R0])    # the per-tile lists
+    assert _C._r_hint[dev] == R0
+
+
 def test_colors_and_cov_paths():
     sc, _ = cases.case("s_deg3")
     d = to_device(sc)
