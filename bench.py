@@ -211,13 +211,18 @@ def run_ours(args, rank, world, local_rank):
         flat = gsr_dp.FlatGrads({k: tuple(t[k].shape) for k in keep}, dev)
         exchange = gsr_dp.FactorExchange(1, P_GAUSS, dev, world) if args.dp_exchange == "factors" else None
 
+    want = {"loss": False}
+
     def render_backward(src):
         leaves = {k: src[k].detach().requires_grad_(True) for k in LEAVES}
         m2 = torch.zeros_like(leaves["means3D"], requires_grad=True)
         color, radii = raster(means3D=leaves["means3D"], means2D=m2, opacities=leaves["opacities"], shs=leaves["sh"],
                               scales=leaves["scales"], rotations=leaves["rotations"])
-        loss = (color * dpix).sum()
-        loss.backward()
+        # The upstream gradient dL/dpixel is handed to the backward directly, as the reference arm does
+        # (ref.backward(dL_dpix)); the step's scalar result <color, dL_dpix> is only formed where it is read back
+        # (the e2e leg).
+        loss = torch.dot(color.detach().view(-1), dpix.view(-1)) if want["loss"] else None
+        color.backward(dpix)
         stats["radii"] = radii
         return loss, {k: leaves[k].grad for k in LEAVES}
 
@@ -303,6 +308,7 @@ def run_ours(args, rank, world, local_rank):
                 prefetch(s_ + 1)
             b = s_ & 1
             cur.wait_event(ready[b])
+            want["loss"] = True
             loss, _ = step(bufs[b])
             consumed[b].record(cur)
             loss_host.copy_(loss.detach().reshape(1), non_blocking=True)

@@ -124,7 +124,7 @@ def test_speculative_forward_hit_miss_and_overflow_guard():
     hit, a miss (hint far too small: the device-side guard must keep the kernels from touching the short buffer)
     and the no-hint first call all return the same bits."""
     from diff_gaussian_rasterization import _C
-    sc = S.scene_S(20000, 640, 360, seed=8, M=16, sh_degree=3)
+    sc = S.scene_S(150000, 640, 360, seed=8, M=16, sh_degree=3)
     d = to_device(sc)
     e = torch.Tensor([])
     dev = d["means3D"].device.index
