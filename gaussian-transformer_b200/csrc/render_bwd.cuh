@@ -133,7 +133,12 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
         const float4 col = lds128(addr + 32);
         float2 d, pp;  // (dx, dy), (dx*A, dy*C)
         const float power = gauss_power2(make_float2(a.x, a.y), npix, make_float2(a.z, a.w), b.x, d, pp);
-        const float G = expf(power);
+        // exp(power) as ex2.approx(power * log2 e): 2 instructions instead of expf's 10.  Relative error ~1e-6
+        // (|power| <= ~10 times one rounding of the product, plus 2 ulp of ex2.approx): far inside the gradient
+        // tolerance; an alpha within 1e-6 of 1/255 may be classified differently from the forward (a few dozen
+        // pixel-Gaussian pairs per frame, each worth < 0.4 % of one pixel's contribution).  The forward keeps expf.
+        float G;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(G) : "f"(power * 1.4426950408889634f));
         const float alpha = fminf(0.99f, __fmul_rn(b.y, G));
         // same acceptance as the forward (backward.cu:488-497): behind the last contributor, power > 0 and
         // alpha < 1/255 are skipped
@@ -146,8 +151,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
         //    once per Gaussian in preprocess_bwd instead of once per (pixel, Gaussian) pair.
         const float om = __fsub_rn(1.0f, alpha);  // alpha <= 0.99 => om in [0.01, 1]
         float rinv;
-        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rinv) : "f"(om));
-        rinv = fmaf(rinv, fmaf(-om, rinv, 1.0f), rinv);  // one Newton step: within 1 ulp of 1/om
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rinv) : "f"(om));  // 1 ulp; T picks up <= ~1e-7 per list entry
         const float Tn = T * rinv;
         const float cd = fmaf(col.z, dLp2, fmaf(col.y, dLp1, col.x * dLp0));  // <colour, dLp>
         const float Sn = fmaf(last_alpha, lcd, (1.f - last_alpha) * S);

@@ -143,9 +143,12 @@ def test_speculative_forward_hit_miss_and_overflow_guard():
         pytest.skip("scene too sparse to overflow the minimum capacity")
     R2, c2, radii2, _, b2, i2 = fwd()
     assert R0 == R1 == R2
+    N = sc["W"] * sc["H"]
     for c, r, b, i in ((c1, radii1, b1, i1), (c2, radii2, b2, i2)):
-        assert torch.equal(c, c0) and torch.equal(r, radii0) and torch.equal(i, i0)
+        assert torch.equal(c, c0)
+        assert torch.equal(r, radii0)
         assert torch.equal(b[:4 * R0], b0[:4 * R0])    # the per-tile lists
+        assert torch.equal(i[:8 * N], i0[:8 * N])      # final_T, n_contrib (the rest has uninitialised padding)
     assert _C._r_hint[dev] == R0
 
 
