@@ -89,6 +89,7 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
   __syncthreads();
   const int seg = blockIdx.x * RS_TILE + w * RS_SEG;
   uint32_t key[RS_ROUNDS], val[RS_ROUNDS];
+  unsigned grp[RS_ROUNDS];  // lanes of this round that share the lane's digit (match.any is slow: done once)
   const unsigned lt = (1u << lane) - 1u;
   // phase 1: load the warp's segment (in order) and count digits
 #pragma unroll
@@ -99,8 +100,10 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
     val[k] = ok ? (vals_in ? __ldg(vals_in + i) : (uint32_t)i) : 0u;
     const uint32_t d = (key[k] >> shift) & 255u;
     const unsigned act = __ballot_sync(0xffffffffu, ok);
+    grp[k] = 0u;
     if (ok) {
       const unsigned m = __match_any_sync(act, d);
+      grp[k] = m;
       if ((m & lt) == 0u) cnt[w][d] += __popc(m);  // leader of its digit group; digits are distinct across leaders
     }
     __syncwarp();
@@ -141,9 +144,8 @@ __global__ void __launch_bounds__(RS_THREADS) radix_scatter_kernel(const uint32_
     const int i = seg + k * 32 + lane;
     const bool ok = i < n;
     const uint32_t d = (key[k] >> shift) & 255u;
-    const unsigned act = __ballot_sync(0xffffffffu, ok);
     if (ok) {
-      const unsigned m = __match_any_sync(act, d);
+      const unsigned m = grp[k];
       const uint32_t pos = cnt[w][d] + __popc(m & lt);
       keys_out[pos] = key[k];
       vals_out[pos] = val[k];
