@@ -111,6 +111,12 @@ int check_inputs(const gsr_inputs* in) {
     if (in->D < 0 || in->D > 3 || (in->D + 1) * (in->D + 1) > in->M)
       return fail(GSR_ERR_INVALID, "sh degree does not fit the number of coefficients");
     if (!in->campos) return fail(GSR_ERR_INVALID, "campos must not be NULL");
+    if (in->sh_rest) {
+      if (in->M != 16 && in->M != 4)
+        return fail(GSR_ERR_INVALID, "split SH storage (sh_rest) is built for M = 16 and M = 4; concatenate otherwise");
+      if (!aligned16(in->sh) || !aligned16(in->sh_rest))
+        return fail(GSR_ERR_INVALID, "split SH storage: sh and sh_rest must be 16-byte aligned");
+    }
   }
   if (!in->cov3D_precomp) {
     if (!in->scales || !in->rotations)
@@ -237,19 +243,20 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   if (plan.n_bands == 0) return fail(GSR_ERR_INVALID, "image wider than 32768 pixels is not supported");
   GSR_CUDA(cudaMemsetAsync(im.ctrl, 0, 4 * CTRL_WORDS, stream), "memset ctrl");
   const int K = (in->D + 1) * (in->D + 1);
-  const bool vec_sh = in->sh && !in->colors_precomp && ((K * 3) % 4 == 0) && ((in->M * 12) % 16 == 0) &&
+  const float* sh_rest = in->colors_precomp ? nullptr : in->sh_rest;
+  const bool vec_sh = in->sh && !sh_rest && !in->colors_precomp && ((K * 3) % 4 == 0) && ((in->M * 12) % 16 == 0) &&
                       aligned16(in->sh);
   const int blocks = (in->P + 255) / 256;
   {
   ScopedStage prof_(GSR_STAGE_PREPROCESS_FWD, stream);
   if (vec_sh)
     preprocess_fwd_kernel<true><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
-                                                            in->rotations, in->opacities, in->sh,
+                                                            in->rotations, in->opacities, in->sh, nullptr,
                                                             in->colors_precomp, in->cov3D_precomp, cam,
                                                             in->prefiltered, radii, g, im.ctrl);
   else
     preprocess_fwd_kernel<false><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
-                                                             in->rotations, in->opacities, in->sh,
+                                                             in->rotations, in->opacities, in->sh, sh_rest,
                                                              in->colors_precomp, in->cov3D_precomp, cam,
                                                              in->prefiltered, radii, g, im.ctrl);
   GSR_STAGE("preprocess_fwd", in->debug, stream);
@@ -412,11 +419,14 @@ int gsr_backward_blend(const gsr_inputs* in, const void* geom, const void* binni
   return GSR_OK;
 }
 
+}  // extern "C"
+
+namespace {
 // Backward stage 2: accumulators -> gradients of the 3-D parameters (fused preprocess backward).
-int gsr_backward_geometry(const gsr_inputs* in, const int32_t* radii, const void* geom, float* dL_dmeans3D,
-                          float* dL_dmeans2D, float* dL_dsh, float* dL_dcolors, float* dL_dopacity,
-                          float* dL_dscales, float* dL_drotations, float* dL_dcov3D, float* dL_dconic,
-                          void* bwd_scratch, void* stream_) {
+int backward_geometry_impl(const gsr_inputs* in, const int32_t* radii, const void* geom, float* dL_dmeans3D,
+                           float* dL_dmeans2D, float* dL_dsh, float* dL_dsh_rest, float* dL_dcolors,
+                           float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                           float* dL_dconic, void* bwd_scratch, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (int rc = check_inputs(in)) return rc;
   if (in->P == 0) return GSR_OK;
@@ -431,6 +441,10 @@ int gsr_backward_geometry(const gsr_inputs* in, const int32_t* radii, const void
   out.dL_dmeans3D = dL_dmeans3D;
   out.dL_dmeans2D = dL_dmeans2D;
   out.dL_dsh = (in->M > 0) ? dL_dsh : nullptr;
+  out.dL_dsh_rest = dL_dsh_rest;
+  const bool split = in->sh && in->sh_rest && !in->colors_precomp;
+  if (split && out.dL_dsh && !dL_dsh_rest)
+    return fail(GSR_ERR_INVALID, "gsr_backward: split SH storage needs dL_dsh_rest (gsr_backward_geometry_split)");
   out.dL_dcolors = dL_dcolors;
   out.dL_dopacity = dL_dopacity;
   out.dL_dscales = dL_dscales;
@@ -440,19 +454,29 @@ int gsr_backward_geometry(const gsr_inputs* in, const int32_t* radii, const void
   ScopedStage prof_(GSR_STAGE_PREPROCESS_BWD, stream);
   // staged (coalesced) variant: SH rows of 16 or 4 coefficients and 16-byte aligned arrays; else the generic one
   const bool staged = in->sh && (in->M == 16 || in->M == 4) && aligned16(in->sh) &&
-                      (!out.dL_dsh || aligned16(dL_dsh)) && aligned16(dL_dmeans3D) && aligned16(dL_dmeans2D) &&
+                      (!out.dL_dsh || (aligned16(dL_dsh) && (!split || aligned16(dL_dsh_rest)))) &&
+                      aligned16(dL_dmeans3D) && aligned16(dL_dmeans2D) &&
                       aligned16(dL_dcolors) && aligned16(dL_dscales) && aligned16(dL_dcov3D) &&
                       aligned16(dL_dconic) && aligned16(dL_drotations);
   const int pb_blocks = (in->P + PB_THREADS - 1) / PB_THREADS;
-  if (staged && in->M == 16) {
+  if (split && !staged) return fail(GSR_ERR_INVALID, "split SH storage: gradient outputs must be 16-byte aligned");
+  if (split && in->M == 16) {
+    preprocess_bwd_staged_kernel<16, true><<<pb_blocks, PB_THREADS, PB_THREADS * 45 * 4, stream>>>(
+        in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, in->sh_rest, in->cov3D_precomp, cam,
+        radii, g.g2, bw, out);
+  } else if (split) {
+    preprocess_bwd_staged_kernel<4, true><<<pb_blocks, PB_THREADS, PB_THREADS * 9 * 4 + 16, stream>>>(
+        in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, in->sh_rest, in->cov3D_precomp, cam,
+        radii, g.g2, bw, out);
+  } else if (staged && in->M == 16) {
     const int smem = PB_THREADS * 13 * 16;
-    preprocess_bwd_staged_kernel<16><<<pb_blocks, PB_THREADS, smem, stream>>>(
-        in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, in->cov3D_precomp, cam, radii,
+    preprocess_bwd_staged_kernel<16, false><<<pb_blocks, PB_THREADS, smem, stream>>>(
+        in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, nullptr, in->cov3D_precomp, cam, radii,
         g.g2, bw, out);
   } else if (staged) {
     const int smem = PB_THREADS * 3 * 16;
-    preprocess_bwd_staged_kernel<4><<<pb_blocks, PB_THREADS, smem, stream>>>(
-        in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, in->cov3D_precomp, cam, radii,
+    preprocess_bwd_staged_kernel<4, false><<<pb_blocks, PB_THREADS, smem, stream>>>(
+        in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, nullptr, in->cov3D_precomp, cam, radii,
         g.g2, bw, out);
   } else {
     preprocess_bwd_kernel<<<pb_blocks, PB_THREADS, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
@@ -461,6 +485,25 @@ int gsr_backward_geometry(const gsr_inputs* in, const int32_t* radii, const void
   }
   GSR_STAGE("preprocess_bwd", in->debug, stream);
   return GSR_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int gsr_backward_geometry(const gsr_inputs* in, const int32_t* radii, const void* geom, float* dL_dmeans3D,
+                          float* dL_dmeans2D, float* dL_dsh, float* dL_dcolors, float* dL_dopacity,
+                          float* dL_dscales, float* dL_drotations, float* dL_dcov3D, float* dL_dconic,
+                          void* bwd_scratch, void* stream_) {
+  return backward_geometry_impl(in, radii, geom, dL_dmeans3D, dL_dmeans2D, dL_dsh, nullptr, dL_dcolors, dL_dopacity,
+                                dL_dscales, dL_drotations, dL_dcov3D, dL_dconic, bwd_scratch, stream_);
+}
+
+int gsr_backward_geometry_split(const gsr_inputs* in, const int32_t* radii, const void* geom, float* dL_dmeans3D,
+                                float* dL_dmeans2D, float* dL_dsh, float* dL_dsh_rest, float* dL_dcolors,
+                                float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
+                                float* dL_dconic, void* bwd_scratch, void* stream_) {
+  return backward_geometry_impl(in, radii, geom, dL_dmeans3D, dL_dmeans2D, dL_dsh, dL_dsh_rest, dL_dcolors,
+                                dL_dopacity, dL_dscales, dL_drotations, dL_dcov3D, dL_dconic, bwd_scratch, stream_);
 }
 
 int gsr_backward(const gsr_inputs* in, const int32_t* radii, const void* geom, const void* binning,

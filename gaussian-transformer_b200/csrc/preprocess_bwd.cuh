@@ -23,7 +23,8 @@ namespace gsr {
 struct BwdOut {
   float* dL_dmeans3D;  // (P,3)
   float* dL_dmeans2D;  // (P,3)
-  float* dL_dsh;       // (P,M,3) or NULL
+  float* dL_dsh;       // (P,M,3) or NULL; split SH storage: the DC rows (P,1,3)
+  float* dL_dsh_rest;  // split SH storage: (P,M-1,3), else unused
   float* dL_dcolors;   // (P,3)
   float* dL_dopacity;  // (P)
   float* dL_dscales;   // (P,3)
@@ -250,15 +251,21 @@ __device__ __forceinline__ void store_staged(float* __restrict__ dst, const floa
 
 // Staged variant: SH rows of MT coefficients (3*MT floats, a multiple of 4) with 16-byte aligned sh / dL_dsh and
 // 16-byte aligned (P,3)/(P,6) gradient outputs.  MT = 16 (degree <= 3 storage) or 4 (degree <= 1 storage).
-template <int MT>
+// SPLIT: split SH storage (gsr_inputs.sh_rest): `shs` = DC rows (P,1,3), sh_rest = (P,MT-1,3).  The CTA's 128 rest
+// rows are ONE contiguous block of 128 * 3 * (MT-1) floats, staged flat (row stride 3*(MT-1) words, odd =>
+// conflict-free) and streamed back the same way; the DC row is three plain loads / a staged (P,3)-style store.
+template <int MT, bool SPLIT>
 __global__ void __launch_bounds__(PB_THREADS, 5) preprocess_bwd_staged_kernel(
     int P, int D, const float* __restrict__ means3D, const float* __restrict__ scales,
     const float* __restrict__ rotations, const float4* __restrict__ g1, const float* __restrict__ shs,
-    const float* __restrict__ cov3D_precomp, Cam cam, const int* __restrict__ radii, const float4* __restrict__ g2,
-    BwdView acc, BwdOut out) {
+    const float* __restrict__ sh_rest, const float* __restrict__ cov3D_precomp, Cam cam,
+    const int* __restrict__ radii, const float4* __restrict__ g2, BwdView acc, BwdOut out) {
   constexpr int NF = 3 * MT, F4 = NF / 4, RS4 = F4 | 1;  // row stride in float4, odd => conflict-free 128-bit rows
-  extern __shared__ float4 s_tile[];                     // [PB_THREADS][RS4]
-  __shared__ __align__(16) float s_v3[4][PB_THREADS * 3];  // dL_dmeans3D, dL_dmeans2D, dL_dcolors, dL_dscales
+  constexpr int NR = NF - 3;                             // SPLIT: floats per rest row
+  extern __shared__ float4 s_tile[];                     // [PB_THREADS][RS4], or SPLIT: float [PB_THREADS][NR]
+  float* const s_rest = reinterpret_cast<float*>(s_tile);
+  // dL_dmeans3D, dL_dmeans2D, dL_dcolors, dL_dscales (, SPLIT: dL_dsh DC rows)
+  __shared__ __align__(16) float s_v3[SPLIT ? 5 : 4][PB_THREADS * 3];
   __shared__ __align__(16) float s_cov[PB_THREADS * 6];
   __shared__ uint32_t s_vis[PB_THREADS / 32];
 
@@ -281,17 +288,31 @@ __global__ void __launch_bounds__(PB_THREADS, 5) preprocess_bwd_staged_kernel(
   }
   __syncthreads();
   if (D > 0) {  // coefficient rows of the visible Gaussians, coalesced (degree 0 needs no coefficient)
-    const float4* __restrict__ src4 = reinterpret_cast<const float4*>(shs + (size_t)base * NF);
     // asynchronous global->shared copies (LDGSTS): no register staging, and the copy overlaps the geometry part
     // below, which does not need the coefficients
     const uint32_t tile_addr = (uint32_t)__cvta_generic_to_shared(s_tile);
+    if (SPLIT) {
+      const float* __restrict__ src = sh_rest + (size_t)base * NR;
+      const int nfl = nG * NR, n4 = nfl >> 2;
 #pragma unroll 4
-    for (int j = tid; j < nG * F4; j += PB_THREADS) {
-      const int row = j / F4, col = j - row * F4;
-      if ((s_vis[row >> 5] >> (row & 31)) & 1u)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile_addr + (uint32_t)(row * RS4 + col) * 16u),
-                     "l"(src4 + j)
-                     : "memory");
+      for (int j = tid; j < n4; j += PB_THREADS) {
+        const int r0 = (4 * j) / NR, r1 = (4 * j + 3) / NR;  // a 16-byte chunk touches one or two rows
+        if (((s_vis[r0 >> 5] >> (r0 & 31)) | (s_vis[r1 >> 5] >> (r1 & 31))) & 1u)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile_addr + (uint32_t)j * 16u),
+                       "l"(reinterpret_cast<const float4*>(src) + j)
+                       : "memory");
+      }
+      for (int j = (n4 << 2) + tid; j < nfl; j += PB_THREADS) s_rest[j] = __ldg(src + j);  // last CTA's tail
+    } else {
+      const float4* __restrict__ src4 = reinterpret_cast<const float4*>(shs + (size_t)base * NF);
+#pragma unroll 4
+      for (int j = tid; j < nG * F4; j += PB_THREADS) {
+        const int row = j / F4, col = j - row * F4;
+        if ((s_vis[row >> 5] >> (row & 31)) & 1u)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile_addr + (uint32_t)(row * RS4 + col) * 16u),
+                       "l"(src4 + j)
+                       : "memory");
+      }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
   }
@@ -318,7 +339,11 @@ __global__ void __launch_bounds__(PB_THREADS, 5) preprocess_bwd_staged_kernel(
     const uint32_t flags = __float_as_uint(__ldg(&g2[i].w));
     const float dRGB[3] = {(flags & 1u) ? 0.f : A.x, (flags & 2u) ? 0.f : A.y, (flags & 4u) ? 0.f : A.z};
     float v[NF];
-    if (D > 0) {
+    if (D > 0 && SPLIT) {
+      v[0] = __ldg(shs + 3 * I); v[1] = __ldg(shs + 3 * I + 1); v[2] = __ldg(shs + 3 * I + 2);
+#pragma unroll
+      for (int k = 0; k < NR; k++) v[3 + k] = s_rest[tid * NR + k];
+    } else if (D > 0) {
 #pragma unroll
       for (int k = 0; k < F4; k++) {
         const float4 q = row4[k];
@@ -331,11 +356,23 @@ __global__ void __launch_bounds__(PB_THREADS, 5) preprocess_bwd_staged_kernel(
     float ddir[3];
     sh_backward_inplace<NF>(D, v, dox / len, doy / len, doz / len, dRGB, ddir);
     dir_backward(dox, doy, doz, ddir, o.dm);
+    if (SPLIT) {
+      s_v3[SPLIT ? 4 : 0][3 * tid] = v[0]; s_v3[SPLIT ? 4 : 0][3 * tid + 1] = v[1]; s_v3[SPLIT ? 4 : 0][3 * tid + 2] = v[2];
 #pragma unroll
-    for (int k = 0; k < F4; k++) row4[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+      for (int k = 0; k < NR; k++) s_rest[tid * NR + k] = v[3 + k];
+    } else {
+#pragma unroll
+      for (int k = 0; k < F4; k++) row4[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+    }
   } else if (in_range) {
+    if (SPLIT) {
+      s_v3[SPLIT ? 4 : 0][3 * tid] = 0.f; s_v3[SPLIT ? 4 : 0][3 * tid + 1] = 0.f; s_v3[SPLIT ? 4 : 0][3 * tid + 2] = 0.f;
 #pragma unroll
-    for (int k = 0; k < F4; k++) row4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int k = 0; k < NR; k++) s_rest[tid * NR + k] = 0.f;
+    } else {
+#pragma unroll
+      for (int k = 0; k < F4; k++) row4[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
   }
   if (in_range) {
 #pragma unroll
@@ -352,7 +389,12 @@ __global__ void __launch_bounds__(PB_THREADS, 5) preprocess_bwd_staged_kernel(
     __stcs(reinterpret_cast<float4*>(out.dL_drot) + I, make_float4(o.dq[0], o.dq[1], o.dq[2], o.dq[3]));
   }
   __syncthreads();
-  if (out.dL_dsh != nullptr) {  // dL_dsh rows: nG * F4 contiguous float4 (NULL: the caller exchanges SH factors)
+  if (SPLIT) {
+    if (out.dL_dsh != nullptr) {
+      store_staged(out.dL_dsh_rest + (size_t)base * NR, s_rest, nG * NR, tid);
+      store_staged(out.dL_dsh + (size_t)base * 3, s_v3[SPLIT ? 4 : 0], nG * 3, tid);
+    }
+  } else if (out.dL_dsh != nullptr) {  // dL_dsh rows: nG * F4 contiguous float4 (NULL: the caller exchanges SH factors)
     float4* __restrict__ dst4 = reinterpret_cast<float4*>(out.dL_dsh + (size_t)base * NF);
     for (int j = tid; j < nG * F4; j += PB_THREADS) {
       const int row = j / F4, col = j - row * F4;

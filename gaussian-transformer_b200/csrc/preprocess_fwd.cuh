@@ -117,8 +117,10 @@ __device__ __forceinline__ void sh_basis(int deg, float x, float y, float z, flo
 // rgb = max(sum_k basis[k]*sh[k] + 0.5, 0), clamped flags (forward.cu:63-70).
 // VEC: coefficients fetched as float4 (requires 16-B aligned rows: M*12 % 16 == 0
 // and an aligned base); else scalar read-only loads.
+// sh_rest != nullptr: split storage, sh_row = the Gaussian's DC coefficient (3 floats), sh_rest = its M-1 others.
 template <bool VEC>
-__device__ __forceinline__ void sh_to_rgb(int deg, int M, const float* __restrict__ sh_row, float dx, float dy,
+__device__ __forceinline__ void sh_to_rgb(int deg, int M, const float* __restrict__ sh_row,
+                                          const float* __restrict__ sh_rest, float dx, float dy,
                                           float dz, float& r, float& g, float& b, uint32_t& clamped) {
   float len = sqrtf(dx * dx + dy * dy + dz * dz);
   float x = dx / len, y = dy / len, z = dz / len;
@@ -151,9 +153,10 @@ __device__ __forceinline__ void sh_to_rgb(int deg, int M, const float* __restric
     }
   } else {
     for (int k = 0; k < K; k++) {
-      acc[0] = fmaf(basis[k], __ldg(sh_row + 3 * k), acc[0]);
-      acc[1] = fmaf(basis[k], __ldg(sh_row + 3 * k + 1), acc[1]);
-      acc[2] = fmaf(basis[k], __ldg(sh_row + 3 * k + 2), acc[2]);
+      const float* c = (sh_rest != nullptr && k > 0) ? sh_rest + 3 * (k - 1) : sh_row + 3 * k;
+      acc[0] = fmaf(basis[k], __ldg(c), acc[0]);
+      acc[1] = fmaf(basis[k], __ldg(c + 1), acc[1]);
+      acc[2] = fmaf(basis[k], __ldg(c + 2), acc[2]);
     }
   }
   (void)M;
@@ -169,7 +172,8 @@ template <bool VEC_SH>
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
     int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
     const float* __restrict__ rotations, const float* __restrict__ opacities, const float* __restrict__ shs,
-    const float* __restrict__ colors_precomp, const float* __restrict__ cov3D_precomp, Cam cam, int prefiltered,
+    const float* __restrict__ sh_rest, const float* __restrict__ colors_precomp,
+    const float* __restrict__ cov3D_precomp, Cam cam, int prefiltered,
     int* __restrict__ radii, GeomView geom, uint32_t* __restrict__ ctrl) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= P) return;
@@ -231,7 +235,10 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
       bl = __ldg(colors_precomp + 3 * (size_t)i + 2);
     } else {
       const float dx = px3 - __ldg(cam.campos), dy = py3 - __ldg(cam.campos + 1), dz = pz3 - __ldg(cam.campos + 2);
-      sh_to_rgb<VEC_SH>(D, M, shs + (size_t)i * M * 3, dx, dy, dz, r, g, bl, clamped);
+      if (sh_rest != nullptr)
+        sh_to_rgb<false>(D, M, shs + (size_t)i * 3, sh_rest + (size_t)i * (M - 1) * 3, dx, dy, dz, r, g, bl, clamped);
+      else
+        sh_to_rgb<VEC_SH>(D, M, shs + (size_t)i * M * 3, nullptr, dx, dy, dz, r, g, bl, clamped);
     }
     out_radius = my_radius;
     o0 = make_float4(mx, my, vz, __int_as_float(my_radius));

@@ -44,7 +44,7 @@ def _ptr(t):
 
 
 def _inputs(P, D, M, W, H, tanfovx, tanfovy, scale_modifier, prefiltered, debug, bg, means3D, sh, colors,
-            opacity, scales, rotations, cov3D, view, proj, campos):
+            opacity, scales, rotations, cov3D, view, proj, campos, sh_rest=None):
     a = _lib.gsr_inputs()
     a.P, a.D, a.M, a.W, a.H = P, D, M, W, H
     a.tanfovx, a.tanfovy, a.scale_modifier = tanfovx, tanfovy, scale_modifier
@@ -52,7 +52,17 @@ def _inputs(P, D, M, W, H, tanfovx, tanfovy, scale_modifier, prefiltered, debug,
     a.bg, a.means3D, a.sh, a.colors_precomp = _ptr(bg), _ptr(means3D), _ptr(sh), _ptr(colors)
     a.opacities, a.scales, a.rotations, a.cov3D_precomp = _ptr(opacity), _ptr(scales), _ptr(rotations), _ptr(cov3D)
     a.viewmatrix, a.projmatrix, a.campos = _ptr(view), _ptr(proj), _ptr(campos)
+    a.sh_rest = _ptr(sh_rest)
     return a
+
+
+def split_sh_ok(dc, rest):
+    """Can (features_dc (P,1,3), features_rest (P,M-1,3)) be passed without concatenation?  (M = 16 or 4, dense
+    float32 CUDA tensors on 16-byte boundaries -- anything else goes through torch.cat.)"""
+    return (dc.is_cuda and rest.is_cuda and dc.dtype == rest.dtype == torch.float32 and dc.dim() == rest.dim() == 3
+            and dc.size(1) == 1 and dc.size(2) == rest.size(2) == 3 and dc.size(0) == rest.size(0)
+            and rest.size(1) + 1 in (4, 16) and dc.is_contiguous() and rest.is_contiguous()
+            and dc.data_ptr() % 16 == 0 and rest.data_ptr() % 16 == 0)
 
 
 def _check_means(means3D):
@@ -67,8 +77,11 @@ _r_hint = {}  # device index -> largest num_rendered seen (sizes the speculative
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
-                        prefiltered, debug):
-    """-> (num_rendered, out_color (3,H,W), radii (P,) int32, geomBuffer, binningBuffer, imgBuffer)."""
+                        prefiltered, debug, sh_rest=None):
+    """-> (num_rendered, out_color (3,H,W), radii (P,) int32, geomBuffer, binningBuffer, imgBuffer).
+
+    sh_rest (extension): split SH storage -- `sh` is features_dc (P,1,3) and sh_rest features_rest (P,M-1,3), read
+    in place instead of through the torch.cat of scene/gaussian_model.py:108-111 (see split_sh_ok)."""
     _check_means(means3D)
     dev = means3D.device
     P, H, W = means3D.size(0), int(image_height), int(image_width)
@@ -79,10 +92,12 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
                     torch.zeros(0, dtype=torch.int32, device=dev), torch.empty(0, **u8), torch.empty(0, **u8),
                     torch.empty(0, **u8))
         M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
+        if sh_rest is not None:
+            M += sh_rest.size(1)
         t = [_f32(x, dev) for x in (background, means3D, sh, colors, opacity, scales, rotations, cov3D_precomp,
                                     viewmatrix, projmatrix, campos)]
         args = _inputs(P, int(degree), M, W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier), prefiltered,
-                       debug, *t)
+                       debug, *t, sh_rest=sh_rest)
         gb, _, ib, _ = _lib.scratch_bytes(P, 0, W, H)
         geom, image = torch.empty(gb, **u8), torch.empty(ib, **u8)
         radii = torch.empty(P, dtype=torch.int32, device=dev)
@@ -115,7 +130,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh,
                                  degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, sh_grad=True,
-                                 factor_sink=None, out=None):
+                                 factor_sink=None, out=None, sh_rest=None):
     """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
 
     sh_grad=False (extension, used by gsr_dp): dL_dsh is not computed and returned as None; the caller rebuilds it
@@ -123,19 +138,25 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     `buffer(P, device) -> (P,3) float32 tensor` and `emit(campos, factors)`; the factors are written into the buffer
     BETWEEN the two backward stages and emit() is called there, so that an exchange it launches overlaps the
     geometry stage.  out (extension): {"means3D" | "sh" | "opacity" | "scales" | "rot": tensor} -- gradients written
-    into the caller's tensors (same shape, float32, contiguous) instead of freshly allocated ones."""
+    into the caller's tensors (same shape, float32, contiguous) instead of freshly allocated ones.  sh_rest
+    (extension): split SH storage as in rasterize_gaussians; dL_dsh is then the pair (dL_dfeatures_dc (P,1,3),
+    dL_dfeatures_rest (P,M-1,3))."""
     _check_means(means3D)
     dev = means3D.device
     P = means3D.size(0)
     H, W = dL_dout_color.size(1), dL_dout_color.size(2)
     M = sh.size(1) if sh is not None and sh.numel() != 0 else 0
+    split = sh_rest is not None
+    if split:
+        M += sh_rest.size(1)
     f32 = dict(dtype=torch.float32, device=dev)
+    g_rest = torch.empty(P, M - 1, 3, **f32) if (split and sh_grad) else None
     g = dict(means3D=torch.empty(P, 3, **f32), means2D=torch.empty(P, 3, **f32),
-             sh=torch.empty(P, M, 3, **f32) if sh_grad else None,
+             sh=torch.empty(P, 1 if split else M, 3, **f32) if sh_grad else None,
              colors=torch.empty(P, 3, **f32), opacity=torch.empty(P, 1, **f32), scales=torch.empty(P, 3, **f32),
              rot=torch.empty(P, 4, **f32), cov3D=torch.empty(P, 6, **f32), conic=torch.empty(P, 2, 2, **f32))
     for k, t in (out or {}).items():
-        if k not in ("means3D", "sh", "opacity", "scales", "rot") or g[k] is None:
+        if k not in ("means3D", "sh", "opacity", "scales", "rot") or g[k] is None or (k == "sh" and split):
             continue
         if t.shape != g[k].shape or t.dtype != torch.float32 or t.device != dev or not t.is_contiguous():
             raise RuntimeError("out[%r] must be a contiguous float32 tensor of shape %s on %s" % (k, tuple(g[k].shape), dev))
@@ -147,7 +168,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             # opacities are not needed by backward (they live in geomBuffer); pass a valid pointer for the checker
             t[4] = t[1]
             args = _inputs(P, int(degree), M, W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier), False,
-                           debug, *t)
+                           debug, *t, sh_rest=sh_rest)
             dpix = _f32(dL_dout_color, dev)
             _, _, _, wb = _lib.scratch_bytes(P, int(R), W, H)
             work = torch.empty(wb, dtype=torch.uint8, device=dev)
@@ -156,10 +177,21 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                     g["colors"].data_ptr(), g["opacity"].data_ptr(), g["scales"].data_ptr(), g["rot"].data_ptr(),
                     g["cov3D"].data_ptr(), g["conic"].data_ptr())
             bin_ptr = binningBuffer.data_ptr() if binningBuffer.numel() else 0
-            if factor_sink is None:
+            if split:
+                outs = outs[:3] + (_ptr(g_rest) if sh_grad else 0,) + outs[3:]
+                geometry = _lib.lib.gsr_backward_geometry_split
+            else:
+                geometry = _lib.lib.gsr_backward_geometry
+            if factor_sink is None and not split:
                 _lib.check(_lib.lib.gsr_backward(ctypes.byref(args), radii.data_ptr(), geomBuffer.data_ptr(), bin_ptr,
                                                  imageBuffer.data_ptr(), int(R), dpix.data_ptr(), *outs,
                                                  work.data_ptr(), stream))
+            elif factor_sink is None:
+                _lib.check(_lib.lib.gsr_backward_blend(ctypes.byref(args), geomBuffer.data_ptr(), bin_ptr,
+                                                       imageBuffer.data_ptr(), int(R), dpix.data_ptr(),
+                                                       work.data_ptr(), stream))
+                _lib.check(geometry(ctypes.byref(args), radii.data_ptr(), geomBuffer.data_ptr(), *outs,
+                                    work.data_ptr(), stream))
             else:
                 _lib.check(_lib.lib.gsr_backward_blend(ctypes.byref(args), geomBuffer.data_ptr(), bin_ptr,
                                                        imageBuffer.data_ptr(), int(R), dpix.data_ptr(),
@@ -170,8 +202,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 _lib.check(_lib.lib.gsr_backward_sh_factors(P, geomBuffer.data_ptr(), work.data_ptr(),
                                                             fac.data_ptr(), stream))
                 factor_sink.emit(campos.detach().reshape(3), fac)
-                _lib.check(_lib.lib.gsr_backward_geometry(ctypes.byref(args), radii.data_ptr(),
-                                                          geomBuffer.data_ptr(), *outs, work.data_ptr(), stream))
+                _lib.check(geometry(ctypes.byref(args), radii.data_ptr(), geomBuffer.data_ptr(), *outs,
+                                    work.data_ptr(), stream))
     elif factor_sink is not None:
         factor_sink.emit(campos.detach().reshape(3), factor_sink.buffer(0, dev))
     if P == 0 and out:
@@ -179,7 +211,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             if g.get(k) is not None:
                 g[k].zero_()
     rasterize_gaussians_backward.last_dL_dconic = g["conic"]  # exposed for the parity tests only
-    return (g["means2D"], g["colors"], g["opacity"], g["means3D"], g["cov3D"], g["sh"], g["scales"], g["rot"])
+    g_sh = (g["sh"], g_rest) if split else g["sh"]
+    return (g["means2D"], g["colors"], g["opacity"], g["means3D"], g["cov3D"], g_sh, g["scales"], g["rot"])
 
 
 def sh_color_factors(geomBuffer, dL_dcolors):

@@ -80,7 +80,8 @@ def _take_out():
 
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, settings):
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, settings,
+                sh_rest=None):
         s = settings
         call = (s.bg, means3D, colors_precomp, opacities, scales, rotations, s.scale_modifier, cov3Ds_precomp,
                 s.viewmatrix, s.projmatrix, s.tanfovx, s.tanfovy, s.image_height, s.image_width, sh, s.sh_degree,
@@ -89,7 +90,7 @@ class _RasterizeGaussians(torch.autograd.Function):
                          "\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.") \
             if s.debug else None
         try:
-            num_rendered, color, radii, geom, binning, img = _C.rasterize_gaussians(*call)
+            num_rendered, color, radii, geom, binning, img = _C.rasterize_gaussians(*call, sh_rest=sh_rest)
         except Exception:
             if dump:
                 dump()
@@ -97,14 +98,15 @@ class _RasterizeGaussians(torch.autograd.Function):
         ctx.raster_settings = s
         ctx.num_rendered = num_rendered
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning,
-                              img)
+                              img, sh_rest)
         ctx.mark_non_differentiable(radii)
         return color, radii
 
     @staticmethod
     def backward(ctx, grad_color, _grad_radii):
         s = ctx.raster_settings
-        colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img = ctx.saved_tensors
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img,
+         sh_rest) = ctx.saved_tensors
         call = (s.bg, means3D, radii, colors_precomp, scales, rotations, s.scale_modifier, cov3Ds_precomp,
                 s.viewmatrix, s.projmatrix, s.tanfovx, s.tanfovy, grad_color, sh, s.sh_degree, s.campos, geom,
                 ctx.num_rendered, binning, img, s.debug)
@@ -116,17 +118,29 @@ class _RasterizeGaussians(torch.autograd.Function):
             sink = _ListSink(sink)
         try:
             (g_means2D, g_colors, g_opac, g_means3D, g_cov3D, g_sh, g_scales,
-             g_rot) = _C.rasterize_gaussians_backward(*call, sh_grad=sink is None, factor_sink=sink, out=_take_out())
+             g_rot) = _C.rasterize_gaussians_backward(*call, sh_grad=sink is None, factor_sink=sink, out=_take_out(),
+                                                      sh_rest=sh_rest)
         except Exception:
             if dump:
                 dump()
             raise
+        g_rest = None
+        if sh_rest is not None:
+            g_sh, g_rest = g_sh if g_sh is not None else (None, None)
         # order of forward's inputs; the settings tuple gets None (DGR __init__.py:143-153)
-        return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None
+        return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None, g_rest
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
                         raster_settings):
+    """`sh` may also be the pair (features_dc (P,1,3), features_rest (P,M-1,3)) of scene/gaussian_model.py:108-111:
+    the kernels then read (and write the gradients of) the two arrays in place instead of their torch.cat."""
+    if isinstance(sh, (tuple, list)):
+        dc, rest = sh
+        if _C.split_sh_ok(dc, rest):
+            return _RasterizeGaussians.apply(means3D, means2D, dc, colors_precomp, opacities, scales, rotations,
+                                             cov3Ds_precomp, raster_settings, rest)
+        sh = torch.cat((dc, rest), dim=1)
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
                                      cov3Ds_precomp, raster_settings)
 

@@ -20,7 +20,7 @@ class gsr_inputs(ctypes.Structure):
         ("bg", ctypes.c_void_p), ("means3D", ctypes.c_void_p), ("sh", ctypes.c_void_p),
         ("colors_precomp", ctypes.c_void_p), ("opacities", ctypes.c_void_p), ("scales", ctypes.c_void_p),
         ("rotations", ctypes.c_void_p), ("cov3D_precomp", ctypes.c_void_p), ("viewmatrix", ctypes.c_void_p),
-        ("projmatrix", ctypes.c_void_p), ("campos", ctypes.c_void_p),
+        ("projmatrix", ctypes.c_void_p), ("campos", ctypes.c_void_p), ("sh_rest", ctypes.c_void_p),
     ]
 
 
@@ -37,7 +37,7 @@ EXPORTS = (
     "gsr_sh_color_factors", "gsr_sh_grad_from_factors", "gsr_knn_scratch_bytes", "gsr_knn_dist2",
     "gsr_loss_scratch_bytes", "gsr_l1_ssim_loss",
     "gsr_backward_blend", "gsr_backward_geometry", "gsr_backward_sh_factors",
-    "gsr_adam_step", "gsr_forward",
+    "gsr_adam_step", "gsr_forward", "gsr_backward_geometry_split",
 )
 STAGES = ("preprocess_fwd", "depth_sort", "bin_count", "bin_scatter", "render_fwd", "render_bwd", "preprocess_bwd")
 
@@ -61,6 +61,7 @@ def load(path=LIB_PATH):
     lib.gsr_backward.argtypes = [inp, vp, vp, vp, vp, i64, vp] + [vp] * 9 + [vp, vp]
     lib.gsr_backward_blend.argtypes = [inp, vp, vp, vp, i64, vp, vp, vp]
     lib.gsr_backward_geometry.argtypes = [inp, vp, vp] + [vp] * 9 + [vp, vp]
+    lib.gsr_backward_geometry_split.argtypes = [inp, vp, vp] + [vp] * 10 + [vp, vp]
     lib.gsr_backward_sh_factors.argtypes = [i32, vp, vp, vp, vp]
     lib.gsr_adam_step.argtypes = [i32, vp, ctypes.c_double, ctypes.c_double, ctypes.c_double, vp]
     lib.gsr_mark_visible.argtypes = [i32, vp, vp, vp, vp, vp]

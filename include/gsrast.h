@@ -73,6 +73,10 @@ typedef struct gsr_inputs {
   const float* viewmatrix;
   const float* projmatrix;
   const float* campos;
+  /* Optional split SH storage (scene/gaussian_model.py:108-111 keeps _features_dc (P,1,3) and _features_rest
+   * (P,M-1,3) and concatenates them for every render): when sh_rest is non-NULL, `sh` is the DC array and sh_rest
+   * the rest; M is still the total number of coefficients.  NULL = `sh` is the concatenated (P,M,3) array. */
+  const float* sh_rest;
 } gsr_inputs;
 
 /* Library version (major*10000 + minor*100 + patch) and the SM architecture the
@@ -160,6 +164,14 @@ GSR_API int gsr_backward_geometry(const gsr_inputs* in, const int32_t* radii, co
                                   float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dsh, float* dL_dcolors,
                                   float* dL_dopacity, float* dL_dscales, float* dL_drotations, float* dL_dcov3D,
                                   float* dL_dconic, void* bwd_scratch, void* stream);
+
+/* gsr_backward_geometry with split SH gradients (in->sh_rest non-NULL): dL_dsh receives the DC rows (P,1,3) and
+ * dL_dsh_rest the rest (P,M-1,3) -- what autograd would hand back through the torch.cat of get_features. */
+GSR_API int gsr_backward_geometry_split(const gsr_inputs* in, const int32_t* radii, const void* geom,
+                                        float* dL_dmeans3D, float* dL_dmeans2D, float* dL_dsh, float* dL_dsh_rest,
+                                        float* dL_dcolors, float* dL_dopacity, float* dL_dscales,
+                                        float* dL_drotations, float* dL_dcov3D, float* dL_dconic,
+                                        void* bwd_scratch, void* stream);
 
 /* Data-parallel SH gradient exchange (no reference counterpart: the reference is single-GPU; this serves the
  * view-sharded path of SURVEY.md section 8e).  For one view, dL/dsh(i,k,c) = basis_k(dir_i) * f(i,c) with

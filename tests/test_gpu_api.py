@@ -152,6 +152,30 @@ def test_speculative_forward_hit_miss_and_overflow_guard():
     assert _C._r_hint[dev] == R0
 
 
+@pytest.mark.parametrize("P,M,deg", [(3001, 16, 3), (3001, 16, 1), (2048, 4, 1), (700, 9, 2), (513, 16, 0)])
+def test_split_sh_matches_concatenated(P, M, deg):
+    """shs=(features_dc, features_rest): same bits forward, same gradients as through torch.cat (SURVEY 8f rank 3;
+    M = 9 is not built and must fall back to the concatenation transparently)."""
+    sc = S.scene_S(P, 320, 208, seed=12, M=M, sh_degree=deg)
+    d = to_device(sc)
+    dpix = torch.from_numpy(S.upstream_grad(sc["W"], sc["H"], 12)).cuda()
+    res = []
+    for split in (False, True):
+        m3, op, scl, rot = (_leaf(d[k]) for k in ("means3D", "opacities", "scales", "rotations"))
+        dc, rest = _leaf(d["sh"][:, :1].contiguous()), _leaf(d["sh"][:, 1:].contiguous())
+        shs = (dc, rest) if split else torch.cat((dc, rest), dim=1)
+        color, radii = _module(d)(means3D=m3, means2D=torch.zeros_like(m3), opacities=op, shs=shs, scales=scl,
+                                  rotations=rot)
+        (color * dpix).sum().backward()
+        res.append((color.detach(), radii, dc.grad, rest.grad, m3.grad, op.grad, scl.grad, rot.grad))
+    a, b = res
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    assert float(a[2].abs().max()) > 0 and (deg == 0 or float(a[3].abs().max()) > 0)
+    for x, y in zip(a[2:], b[2:]):
+        assert x.shape == y.shape
+        assert rel_err(np_(y), np_(x)) <= 1e-4  # order of the blend atomics only
+
+
 def test_colors_and_cov_paths():
     sc, _ = cases.case("s_deg3")
     d = to_device(sc)

@@ -102,6 +102,22 @@ def main():
             opt.zero_grad(set_to_none=True)
         return it
 
+    if os.environ.get("GSR_TIMELINE"):
+        from torch.profiler import ProfilerActivity, profile
+        it = make("+adam")
+        for _ in range(3):
+            it()
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as tp:
+            it()
+            it()
+            torch.cuda.synchronize()
+        ev = sorted((e for e in tp.events() if e.device_type.name == "CUDA"), key=lambda e: e.time_range.start)
+        t0 = ev[0].time_range.start
+        with open(os.environ["GSR_TIMELINE"], "w") as f:
+            for e in ev:
+                f.write("%9.1f %8.1f  %s\n" % (e.time_range.start - t0, e.time_range.end - e.time_range.start, e.name[:100]))
+        return
     res = {}
     for kind in ("reference", "raster", "+loss", "+adam"):
         it = make(kind)
