@@ -1,0 +1,60 @@
+// csrc/activations.cuh -- the parameter activations in front of the rasterizer:
+// scene/gaussian_model.py:95-106 get_scaling = exp(_scaling), get_rotation = normalize(_rotation),
+// get_opacity = sigmoid(_opacity), as set up at :43-51.  The reference runs them as ~8 elementwise / reduce kernels
+// forward and ~17 backward on every iteration; here each direction is one pass over 32 B per Gaussian.
+// The expressions are the ones torch's CUDA kernels evaluate (sigmoid: 1 / (1 + expf(-x)), exp: expf,
+// F.normalize: x / max(||x||_2, 1e-12)), so that the rasterizer sees the same inputs.
+#pragma once
+#include "common.cuh"
+
+namespace gsr {
+
+// ||q||_2 as torch's norm reduction evaluates a row of 4 on this GPU: sqrt((x^2 + z^2) + (y^2 + w^2)) with every
+// product rounded (established by trying all summation trees against torch.linalg.vector_norm on a B200: this is
+// the only family that matches bit for bit; tests/test_gpu_activations.py keeps checking it).
+__device__ __forceinline__ float quat_norm(float4 q) {
+  return __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(q.x, q.x), __fmul_rn(q.z, q.z)),
+                              __fadd_rn(__fmul_rn(q.y, q.y), __fmul_rn(q.w, q.w))));
+}
+
+__global__ void __launch_bounds__(256) activate_kernel(int P, const float* __restrict__ opacity_raw,
+                                                       const float* __restrict__ scaling_raw,
+                                                       const float4* __restrict__ rotation_raw,
+                                                       float* __restrict__ opacities, float* __restrict__ scales,
+                                                       float4* __restrict__ rotations) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  const size_t I = (size_t)i;
+  opacities[I] = __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-__ldg(opacity_raw + I))));
+#pragma unroll
+  for (int k = 0; k < 3; k++) scales[3 * I + k] = expf(__ldg(scaling_raw + 3 * I + k));
+  const float4 q = __ldg(rotation_raw + I);
+  const float n = fmaxf(quat_norm(q), 1e-12f);
+  rotations[I] = make_float4(__fdiv_rn(q.x, n), __fdiv_rn(q.y, n), __fdiv_rn(q.z, n), __fdiv_rn(q.w, n));
+}
+
+// Chain rule of the three activations; the activated values are recomputed from the raw parameters.
+__global__ void __launch_bounds__(256) activate_bwd_kernel(
+    int P, const float* __restrict__ opacity_raw, const float* __restrict__ scaling_raw,
+    const float4* __restrict__ rotation_raw, const float* __restrict__ g_opac, const float* __restrict__ g_scales,
+    const float4* __restrict__ g_rot, float* __restrict__ d_opacity_raw, float* __restrict__ d_scaling_raw,
+    float4* __restrict__ d_rotation_raw) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  const size_t I = (size_t)i;
+  const float o = __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-__ldg(opacity_raw + I))));
+  d_opacity_raw[I] = __ldg(g_opac + I) * (1.0f - o) * o;  // sigmoid_backward: grad * (1 - y) * y
+#pragma unroll
+  for (int k = 0; k < 3; k++) d_scaling_raw[3 * I + k] = __ldg(g_scales + 3 * I + k) * expf(__ldg(scaling_raw + 3 * I + k));
+  const float4 q = __ldg(rotation_raw + I), g = __ldg(g_rot + I);
+  const float nr = quat_norm(q);
+  const float n = fmaxf(nr, 1e-12f);
+  const float inv = 1.0f / n;
+  const float4 u = make_float4(q.x * inv, q.y * inv, q.z * inv, q.w * inv);
+  // y = q / n: dq = g / n - (norm > eps ? u * <u, g> / n : 0)
+  const float dot = nr > 1e-12f ? (u.x * g.x + u.y * g.y + u.z * g.z + u.w * g.w) : 0.f;
+  d_rotation_raw[I] = make_float4((g.x - u.x * dot) * inv, (g.y - u.y * dot) * inv, (g.z - u.z * dot) * inv,
+                                  (g.w - u.w * dot) * inv);
+}
+
+}  // namespace gsr

@@ -17,6 +17,7 @@
 #include "knn.cuh"
 #include "loss.cuh"
 #include "adam.cuh"
+#include "activations.cuh"
 #include "preprocess_bwd.cuh"
 #include "preprocess_fwd.cuh"
 #include "render_bwd.cuh"
@@ -654,6 +655,42 @@ int gsr_l1_ssim_loss(int32_t C, int32_t H, int32_t W, const float* img, const fl
                                                     (float)(lambda_dssim / n), dL_dimg);
     GSR_STAGE("loss_pass2", 0, stream);
   }
+  return GSR_OK;
+}
+
+// ---- parameter activations in front of the rasterizer
+int gsr_activate(int32_t P, const float* opacity_raw, const float* scaling_raw, const float* rotation_raw,
+                 float* opacities, float* scales, float* rotations, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0) return fail(GSR_ERR_INVALID, "gsr_activate: P < 0");
+  if (P == 0) return GSR_OK;
+  if (!opacity_raw || !scaling_raw || !rotation_raw || !opacities || !scales || !rotations)
+    return fail(GSR_ERR_INVALID, "gsr_activate: NULL pointer");
+  if (!aligned16(rotation_raw) || !aligned16(rotations))
+    return fail(GSR_ERR_INVALID, "gsr_activate: rotation arrays must be 16-byte aligned");
+  activate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, opacity_raw, scaling_raw,
+                                                       reinterpret_cast<const float4*>(rotation_raw), opacities, scales,
+                                                       reinterpret_cast<float4*>(rotations));
+  GSR_STAGE("activate", 0, stream);
+  return GSR_OK;
+}
+
+int gsr_activate_backward(int32_t P, const float* opacity_raw, const float* scaling_raw, const float* rotation_raw,
+                          const float* dL_dopacities, const float* dL_dscales, const float* dL_drotations,
+                          float* dL_dopacity_raw, float* dL_dscaling_raw, float* dL_drotation_raw, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0) return fail(GSR_ERR_INVALID, "gsr_activate_backward: P < 0");
+  if (P == 0) return GSR_OK;
+  if (!opacity_raw || !scaling_raw || !rotation_raw || !dL_dopacities || !dL_dscales || !dL_drotations ||
+      !dL_dopacity_raw || !dL_dscaling_raw || !dL_drotation_raw)
+    return fail(GSR_ERR_INVALID, "gsr_activate_backward: NULL pointer");
+  if (!aligned16(rotation_raw) || !aligned16(dL_drotations) || !aligned16(dL_drotation_raw))
+    return fail(GSR_ERR_INVALID, "gsr_activate_backward: rotation arrays must be 16-byte aligned");
+  activate_bwd_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
+      P, opacity_raw, scaling_raw, reinterpret_cast<const float4*>(rotation_raw), dL_dopacities, dL_dscales,
+      reinterpret_cast<const float4*>(dL_drotations), dL_dopacity_raw, dL_dscaling_raw,
+      reinterpret_cast<float4*>(dL_drotation_raw));
+  GSR_STAGE("activate_bwd", 0, stream);
   return GSR_OK;
 }
 

@@ -38,6 +38,7 @@ EXPORTS = (
     "gsr_loss_scratch_bytes", "gsr_l1_ssim_loss",
     "gsr_backward_blend", "gsr_backward_geometry", "gsr_backward_sh_factors",
     "gsr_adam_step", "gsr_forward", "gsr_backward_geometry_split",
+    "gsr_activate", "gsr_activate_backward",
 )
 STAGES = ("preprocess_fwd", "depth_sort", "bin_count", "bin_scatter", "render_fwd", "render_bwd", "preprocess_bwd")
 
@@ -64,6 +65,8 @@ def load(path=LIB_PATH):
     lib.gsr_backward_geometry_split.argtypes = [inp, vp, vp] + [vp] * 10 + [vp, vp]
     lib.gsr_backward_sh_factors.argtypes = [i32, vp, vp, vp, vp]
     lib.gsr_adam_step.argtypes = [i32, vp, ctypes.c_double, ctypes.c_double, ctypes.c_double, vp]
+    lib.gsr_activate.argtypes = [i32, vp, vp, vp, vp, vp, vp, vp]
+    lib.gsr_activate_backward.argtypes = [i32] + [vp] * 9 + [vp]
     lib.gsr_mark_visible.argtypes = [i32, vp, vp, vp, vp, vp]
     lib.gsr_loss_scratch_bytes.argtypes = [i32, i32, i32, szp]
     lib.gsr_l1_ssim_loss.argtypes = [i32, i32, i32, vp, vp, ctypes.c_float, vp, vp, vp, vp]

@@ -213,6 +213,19 @@ GSR_API int gsr_loss_scratch_bytes(int32_t C, int32_t H, int32_t W, size_t* byte
 GSR_API int gsr_l1_ssim_loss(int32_t C, int32_t H, int32_t W, const float* img, const float* gt,
                              float lambda_dssim, float* out3, float* dL_dimg, void* scratch, void* stream);
 
+/* The parameter activations in front of the rasterizer, one pass per direction over 32 B per Gaussian: replaces
+ * get_opacity = sigmoid(_opacity), get_scaling = exp(_scaling), get_rotation = normalize(_rotation)
+ * (scene/gaussian_model.py:43-51, 95-106) and their autograd replay.  Same expressions as torch's CUDA kernels
+ * (1 / (1 + expf(-x)); expf; x / max(||x||_2, 1e-12)).
+ *   opacity_raw float[P]  scaling_raw float[P*3]  rotation_raw float[P*4] (16-byte aligned), outputs likewise;
+ *   backward: dL_d<activated> in, dL_d<raw> out. */
+GSR_API int gsr_activate(int32_t P, const float* opacity_raw, const float* scaling_raw, const float* rotation_raw,
+                         float* opacities, float* scales, float* rotations, void* stream);
+GSR_API int gsr_activate_backward(int32_t P, const float* opacity_raw, const float* scaling_raw,
+                                  const float* rotation_raw, const float* dL_dopacities, const float* dL_dscales,
+                                  const float* dL_drotations, float* dL_dopacity_raw, float* dL_dscaling_raw,
+                                  float* dL_drotation_raw, void* stream);
+
 /* Fused Adam step over up to 8 parameter groups in ONE launch: replaces the torch.optim.Adam(l, lr=0.0, eps=1e-15)
  * step of scene/gaussian_model.py:149-167 / train.py:126-128 (betas (0.9, 0.999) by default, no weight decay, no
  * amsgrad; torch/optim/adam.py op order, bias corrections in double on the host).  Arrays are device float32 and

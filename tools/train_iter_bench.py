@@ -5,7 +5,9 @@ render, L1 + D-SSIM loss, backward, Adam step over the six groups -- timed with 
               torch + torch.optim.Adam          (what the reference's train.py does)
   raster    : libgsrast rasterizer + torch loss + torch Adam
   +loss     : ... + fused L1/SSIM loss (utils.loss_utils.l1_ssim_loss)
-  +adam     : ... + gsr_optim.FusedAdam          (everything this repository builds)
+  +adam     : ... + gsr_optim.FusedAdam
+  +split    : ... + shs=(features_dc, features_rest) read in place, no torch.cat
+  +act      : ... + gsr_activations.activate (one kernel per direction)   (everything this repository builds)
 
 Synthetic scene S (1M Gaussians, SH degree 3, 1920x1080), ground truth = a perturbed render.  Dev tool; needs a GPU.
 """
@@ -20,6 +22,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path[:0] = [os.path.join(ROOT, "gaussian-transformer_b200"), os.path.join(ROOT, "tests")]
 import gsr_scenes as S  # noqa: E402
 from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer  # noqa: E402
+from gsr_activations import activate  # noqa: E402
 from gsr_optim import FusedAdam  # noqa: E402
 from utils.loss_utils import l1_ssim_loss  # noqa: E402
 
@@ -82,18 +85,21 @@ def main():
         groups = [{"params": [p[k]], "lr": lr, "name": k} for k, lr in
                   (("xyz", 1.6e-4), ("f_dc", 2.5e-3), ("f_rest", 1.25e-4), ("opacity", 0.05), ("scaling", 5e-3),
                    ("rotation", 1e-3))]
-        opt = (FusedAdam if kind == "+adam" else torch.optim.Adam)(groups, lr=0.0, eps=1e-15)
+        opt = (FusedAdam if kind in ("+adam", "+split", "+act") else torch.optim.Adam)(groups, lr=0.0, eps=1e-15)
 
         def it():
-            sh = torch.cat((p["f_dc"], p["f_rest"]), dim=1)             # get_features
-            opac, scl = torch.sigmoid(p["opacity"]), torch.exp(p["scaling"])
-            rot = F.normalize(p["rotation"])
+            sh = (p["f_dc"], p["f_rest"]) if kind in ("+split", "+act") else torch.cat((p["f_dc"], p["f_rest"]), dim=1)
+            if kind == "+act":
+                opac, scl, rot = activate(p["opacity"], p["scaling"], p["rotation"])
+            else:
+                opac, scl = torch.sigmoid(p["opacity"]), torch.exp(p["scaling"])
+                rot = F.normalize(p["rotation"])
             if kind == "reference":
                 img = RefRaster.apply(ref, d, p["xyz"], sh, opac, scl, rot)
             else:
                 m2 = torch.zeros_like(p["xyz"], requires_grad=True)
                 img, _ = raster(means3D=p["xyz"], means2D=m2, opacities=opac, shs=sh, scales=scl, rotations=rot)
-            if kind in ("+loss", "+adam"):
+            if kind in ("+loss", "+adam", "+split", "+act"):
                 loss, _ = l1_ssim_loss(img, gt, LAMBDA)
             else:
                 loss = torch_loss(img, gt, win)
@@ -104,7 +110,7 @@ def main():
 
     if os.environ.get("GSR_TIMELINE"):
         from torch.profiler import ProfilerActivity, profile
-        it = make("+adam")
+        it = make("+act")
         for _ in range(3):
             it()
         torch.cuda.synchronize()
@@ -119,7 +125,7 @@ def main():
                 f.write("%9.1f %8.1f  %s\n" % (e.time_range.start - t0, e.time_range.end - e.time_range.start, e.name[:100]))
         return
     res = {}
-    for kind in ("reference", "raster", "+loss", "+adam"):
+    for kind in ("reference", "raster", "+loss", "+adam", "+split", "+act"):
         it = make(kind)
         for _ in range(3):
             it()
@@ -133,7 +139,7 @@ def main():
         torch.cuda.synchronize()
         res[kind] = a.elapsed_time(b) / n
         print(f"{kind:10s} {res[kind]:7.3f} ms/iteration  ({1000 / res[kind]:6.1f} it/s)", flush=True)
-    print(f"train.py-style iteration, P={P} {W}x{H}: {res['reference'] / res['+adam']:.2f}x the reference stack")
+    print(f"train.py-style iteration, P={P} {W}x{H}: {res['reference'] / res['+act']:.2f}x the reference stack")
 
 
 if __name__ == "__main__":
