@@ -114,10 +114,10 @@ def algorithmic_bytes(P, V, R, N, K, M):
 # summarised in profiles/r01_ncu_full_metrics.txt (a property of the workload, not of the run: bench.py only ever
 # runs C2).  Below the algorithmic bytes wherever list entries and per-Gaussian records are re-read from the L2.
 NCU_DRAM_BYTES_C2 = {
-    "preprocess_fwd": 216.99e6 + 42.09e6,
-    "render_fwd": 65.83e6 + 18.19e6,
-    "render_bwd": 116.69e6 + 6.54e6,
-    "preprocess_bwd": 285.00e6 + 241.79e6,
+    "preprocess_fwd": 216.99e6 + 41.03e6,
+    "render_fwd": 65.69e6 + 18.70e6,
+    "render_bwd": 117.35e6 + 6.70e6,
+    "preprocess_bwd": 285.00e6 + 242.47e6,
 }
 
 
