@@ -118,7 +118,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
             raise RuntimeError("gsrast: point is filtered although prefiltered is set. This shouldn't happen!")
         if R > 0x7FFFFFFF:
             raise RuntimeError(f"gsrast: num_rendered = {R} does not fit a 32-bit int")
-        _r_hint[dev.index] = max(hint, R)
+        _r_hint[dev.index] = max(R, hint - hint // 16)  # follows shrinking scenes too (decays ~6 % per call)
         if R > cap or cap == 0:
             _, bb, _, _ = _lib.scratch_bytes(P, R, W, H)
             binning = torch.empty(bb if R > 0 else 0, **u8)

@@ -119,6 +119,47 @@ def test_factor_exchange_sink_and_staged_backward():
     assert rel_err(np_(fac[0]), np_(want)) <= 1e-3
 
 
+def test_dp_step_factored_two_views_one_rank():
+    """gsr_dp.dp_step_factored with the real rasterizer, two views on one rank (slots 0 and 1 of the exchange, the
+    first view written straight into the flat buffer, the second added): equals the plain sum of both backward
+    passes for all five parameters."""
+    import gsr_dp
+    P, W, H = 3000, 320, 208
+    scs = [S.scene_S(P, W, H, seed=7, M=16, sh_degree=3, yaw_deg=y) for y in (-8.0, 9.0)]
+    ds = [to_device(sc) for sc in scs]
+    dpix = [torch.from_numpy(S.upstream_grad(W, H, 20 + v)).cuda() for v in range(2)]
+    names = {"means3D": "means3D", "sh": "sh", "opacities": "opacities", "scales": "scales", "rotations": "rotations"}
+
+    def run(v, sink_ctx):
+        d = ds[v]
+        leaves = {k: _leaf(d[k]) for k in names}
+        with sink_ctx:
+            color, _ = _module(d)(means3D=leaves["means3D"], means2D=torch.zeros_like(leaves["means3D"]),
+                                  opacities=leaves["opacities"], shs=leaves["sh"], scales=leaves["scales"],
+                                  rotations=leaves["rotations"])
+            color.backward(dpix[v])
+        return {k: leaves[k].grad for k in names}
+
+    plain = [run(v, contextlib.nullcontext()) for v in range(2)]
+    flat = gsr_dp.FlatGrads({k: tuple(ds[0][k].shape) for k in gsr_dp.SMALL_LEAVES}, "cuda")
+    ex = gsr_dp.FactorExchange(2, P, ds[0]["means3D"].device, 1)
+
+    class both:
+        def __init__(self, *c): self.c = c
+        def __enter__(self): [c.__enter__() for c in self.c]
+        def __exit__(self, *e): [c.__exit__(*e) for c in reversed(self.c)]
+
+    for _ in range(2):  # second step: buffers are reused
+        out = gsr_dp.dp_step_factored(
+            lambda v, e: {k: g for k, g in run(v, both(gsr_dp.capture_sh_factors(e), gsr_dp.grads_into(flat))).items()
+                          if k in gsr_dp.SMALL_LEAVES},
+            2, flat, 0, 1, ds[0]["means3D"], 3, 16, exchange=ex)
+    for k in names:
+        want = plain[0][k] + plain[1][k]
+        assert float(want.abs().max()) > 0
+        assert rel_err(np_(out[k]).reshape(want.shape), np_(want)) <= 1e-3, k
+
+
 def test_speculative_forward_hit_miss_and_overflow_guard():
     """gsr_forward launches phase 2 before num_rendered reaches the host, against a buffer sized from a hint: a
     hit, a miss (hint far too small: the device-side guard must keep the kernels from touching the short buffer)
