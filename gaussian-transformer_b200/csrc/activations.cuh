@@ -58,3 +58,28 @@ __global__ void __launch_bounds__(256) activate_bwd_kernel(
 }
 
 }  // namespace gsr
+
+namespace gsr {
+
+// Per-iteration densification statistics (train.py:113-116, scene/gaussian_model.py:405-407), for the Gaussians the
+// view saw (radii > 0):  max_radii2D = max(max_radii2D, radii);  xyz_gradient_accum += ||dL/dmeans2D.xy||;
+// denom += 1.  The reference does this with boolean-mask indexing (a nonzero() host synchronisation, gathers and
+// index_puts); here it is one pass over 28 B per Gaussian with no synchronisation.  The 2-norm is torch's
+// sqrt(x*x + y*y) with both products rounded.
+__global__ void __launch_bounds__(256) densify_stats_kernel(int P, const int* __restrict__ radii,
+                                                            const float* __restrict__ dL_dmeans2D,
+                                                            float* __restrict__ max_radii2D,
+                                                            float* __restrict__ xyz_gradient_accum,
+                                                            float* __restrict__ denom) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= P) return;
+  const int r = __ldg(radii + i);
+  if (r <= 0) return;
+  const size_t I = (size_t)i;
+  max_radii2D[I] = fmaxf(max_radii2D[I], (float)r);
+  const float gx = __ldg(dL_dmeans2D + 3 * I), gy = __ldg(dL_dmeans2D + 3 * I + 1);
+  xyz_gradient_accum[I] = __fadd_rn(xyz_gradient_accum[I], __fsqrt_rn(__fadd_rn(__fmul_rn(gx, gx), __fmul_rn(gy, gy))));
+  denom[I] = __fadd_rn(denom[I], 1.0f);
+}
+
+}  // namespace gsr

@@ -694,6 +694,19 @@ int gsr_activate_backward(int32_t P, const float* opacity_raw, const float* scal
   return GSR_OK;
 }
 
+int gsr_densification_stats(int32_t P, const int32_t* radii, const float* dL_dmeans2D, float* max_radii2D,
+                            float* xyz_gradient_accum, float* denom, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0) return fail(GSR_ERR_INVALID, "gsr_densification_stats: P < 0");
+  if (P == 0) return GSR_OK;
+  if (!radii || !dL_dmeans2D || !max_radii2D || !xyz_gradient_accum || !denom)
+    return fail(GSR_ERR_INVALID, "gsr_densification_stats: NULL pointer");
+  densify_stats_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, radii, dL_dmeans2D, max_radii2D, xyz_gradient_accum,
+                                                            denom);
+  GSR_STAGE("densify_stats", 0, stream);
+  return GSR_OK;
+}
+
 // ---- fused multi-group Adam step
 int gsr_adam_step(int32_t n_groups, const gsr_adam_group* groups, double beta1, double beta2, double eps,
                   void* stream_) {

@@ -38,7 +38,7 @@ EXPORTS = (
     "gsr_loss_scratch_bytes", "gsr_l1_ssim_loss",
     "gsr_backward_blend", "gsr_backward_geometry", "gsr_backward_sh_factors",
     "gsr_adam_step", "gsr_forward", "gsr_backward_geometry_split",
-    "gsr_activate", "gsr_activate_backward",
+    "gsr_activate", "gsr_activate_backward", "gsr_densification_stats",
 )
 STAGES = ("preprocess_fwd", "depth_sort", "bin_count", "bin_scatter", "render_fwd", "render_bwd", "preprocess_bwd")
 
@@ -67,6 +67,7 @@ def load(path=LIB_PATH):
     lib.gsr_adam_step.argtypes = [i32, vp, ctypes.c_double, ctypes.c_double, ctypes.c_double, vp]
     lib.gsr_activate.argtypes = [i32, vp, vp, vp, vp, vp, vp, vp]
     lib.gsr_activate_backward.argtypes = [i32] + [vp] * 9 + [vp]
+    lib.gsr_densification_stats.argtypes = [i32, vp, vp, vp, vp, vp, vp]
     lib.gsr_mark_visible.argtypes = [i32, vp, vp, vp, vp, vp]
     lib.gsr_loss_scratch_bytes.argtypes = [i32, i32, i32, szp]
     lib.gsr_l1_ssim_loss.argtypes = [i32, i32, i32, vp, vp, ctypes.c_float, vp, vp, vp, vp]

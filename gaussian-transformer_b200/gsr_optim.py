@@ -72,3 +72,29 @@ class FusedAdam(torch.optim.Optimizer):
                                         st["exp_avg_sq"].data_ptr(), p.numel(), int(st["step"]), lr)
                     _lib.check(_lib.lib.gsr_adam_step(len(part), arr, betas[0], betas[1], eps, stream))
         return loss
+
+
+@torch.no_grad()
+def densification_stats(radii, viewspace_grad, max_radii2D, xyz_gradient_accum, denom):
+    """train.py:113-116 + GaussianModel.add_densification_stats (scene/gaussian_model.py:405-407) in one kernel and
+    without the boolean-mask host synchronisation:
+
+        visibility_filter = radii > 0
+        max_radii2D[visibility_filter] = torch.max(max_radii2D[visibility_filter], radii[visibility_filter])
+        xyz_gradient_accum[visibility_filter] += torch.norm(viewspace_grad[visibility_filter, :2], dim=-1, keepdim=True)
+        denom[visibility_filter] += 1
+
+    radii (P,) int32 and viewspace_grad (P,3) = screenspace_points.grad as the rasterizer returns them; the three
+    statistics tensors ((P,), (P,1), (P,1) float32, contiguous) are updated in place."""
+    P = radii.size(0)
+    for t, n in ((viewspace_grad, 3 * P), (max_radii2D, P), (xyz_gradient_accum, P), (denom, P)):
+        if not t.is_cuda or t.dtype != torch.float32 or not t.is_contiguous() or t.numel() != n:
+            raise RuntimeError("densification_stats: dense float32 CUDA tensors of P rows expected")
+    if not radii.is_cuda or radii.dtype != torch.int32 or not radii.is_contiguous():
+        raise RuntimeError("densification_stats: radii must be the rasterizer's int32 CUDA tensor")
+    if P:
+        with torch.cuda.device(radii.device):
+            _lib.check(_lib.lib.gsr_densification_stats(P, radii.data_ptr(), viewspace_grad.data_ptr(),
+                                                        max_radii2D.data_ptr(), xyz_gradient_accum.data_ptr(),
+                                                        denom.data_ptr(),
+                                                        torch.cuda.current_stream(radii.device).cuda_stream))

@@ -226,6 +226,14 @@ GSR_API int gsr_activate_backward(int32_t P, const float* opacity_raw, const flo
                                   const float* dL_drotations, float* dL_dopacity_raw, float* dL_dscaling_raw,
                                   float* dL_drotation_raw, void* stream);
 
+/* Per-iteration densification statistics for the Gaussians the view saw (radii > 0): replaces the boolean-mask
+ * updates of train.py:113-116 and GaussianModel.add_densification_stats (scene/gaussian_model.py:405-407) --
+ * max_radii2D = max(max_radii2D, radii), xyz_gradient_accum += ||dL_dmeans2D.xy||_2, denom += 1 -- without their
+ * nonzero() host synchronisation.  radii int32[P] and dL_dmeans2D float[P*3] as returned by the rasterizer;
+ * max_radii2D, xyz_gradient_accum, denom float[P], updated in place. */
+GSR_API int gsr_densification_stats(int32_t P, const int32_t* radii, const float* dL_dmeans2D, float* max_radii2D,
+                                    float* xyz_gradient_accum, float* denom, void* stream);
+
 /* Fused Adam step over up to 8 parameter groups in ONE launch: replaces the torch.optim.Adam(l, lr=0.0, eps=1e-15)
  * step of scene/gaussian_model.py:149-167 / train.py:126-128 (betas (0.9, 0.999) by default, no weight decay, no
  * amsgrad; torch/optim/adam.py op order, bias corrections in double on the host).  Arrays are device float32 and

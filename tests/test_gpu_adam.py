@@ -122,3 +122,25 @@ def test_errors():
     p.grad = torch.ones(3)
     with pytest.raises(RuntimeError):
         FusedAdam([p]).step()
+
+
+def test_densification_stats_match_reference_updates():
+    """gsr_optim.densification_stats vs the boolean-mask statements of train.py:113-116 / gaussian_model.py:405-407."""
+    from gsr_optim import densification_stats
+    P = 100003
+    g = torch.Generator(device="cuda").manual_seed(7)
+    radii = torch.randint(-1, 40, (P,), device="cuda", generator=g, dtype=torch.int32).clamp_min(0)
+    grad = torch.randn(P, 3, device="cuda", generator=g) * 1e-4
+    state = [torch.rand(P, device="cuda", generator=g) * 30, torch.rand(P, 1, device="cuda", generator=g),
+             torch.randint(0, 50, (P, 1), device="cuda", generator=g).float()]
+    want = [t.clone() for t in state]
+    vis = radii > 0
+    want[0][vis] = torch.max(want[0][vis], radii[vis])
+    want[1][vis] += torch.norm(grad[vis, :2], dim=-1, keepdim=True)
+    want[2][vis] += 1
+    densification_stats(radii, grad, *state)
+    assert torch.equal(state[0], want[0]) and torch.equal(state[2], want[2])
+    torch.testing.assert_close(state[1], want[1], rtol=1e-6, atol=0)
+    assert int((state[1] != want[1]).sum()) == 0  # torch's 2-element norm is sqrt(x*x + y*y), products rounded
+    with pytest.raises(RuntimeError):
+        densification_stats(radii.long(), grad, *state)

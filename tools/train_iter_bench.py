@@ -7,7 +7,10 @@ render, L1 + D-SSIM loss, backward, Adam step over the six groups -- timed with 
   +loss     : ... + fused L1/SSIM loss (utils.loss_utils.l1_ssim_loss)
   +adam     : ... + gsr_optim.FusedAdam
   +split    : ... + shs=(features_dc, features_rest) read in place, no torch.cat
-  +act      : ... + gsr_activations.activate (one kernel per direction)   (everything this repository builds)
+  +act      : ... + gsr_activations.activate (one kernel per direction)
+  +stats    : ... + gsr_optim.densification_stats (no boolean-mask host sync)   (everything this repository builds)
+
+Every configuration also keeps the per-iteration densification statistics of train.py:113-116.
 
 Synthetic scene S (1M Gaussians, SH degree 3, 1920x1080), ground truth = a perturbed render.  Dev tool; needs a GPU.
 """
@@ -23,10 +26,11 @@ sys.path[:0] = [os.path.join(ROOT, "gaussian-transformer_b200"), os.path.join(RO
 import gsr_scenes as S  # noqa: E402
 from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer  # noqa: E402
 from gsr_activations import activate  # noqa: E402
-from gsr_optim import FusedAdam  # noqa: E402
+from gsr_optim import FusedAdam, densification_stats  # noqa: E402
 from utils.loss_utils import l1_ssim_loss  # noqa: E402
 
 P = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
+FUSED = ("raster", "+loss", "+adam", "+split", "+act", "+stats")  # cumulative
 W, H, DEG, M, LAMBDA = 1920, 1080, 3, 16, 0.2
 
 
@@ -45,17 +49,18 @@ class RefRaster(torch.autograd.Function):
     """The unmodified reference rasterizer behind autograd (its own torch glue is not built here)."""
 
     @staticmethod
-    def forward(ctx, ref, d, means3D, sh, opacities, scales, rotations):
+    def forward(ctx, ref, d, means3D, means2D, sh, opacities, scales, rotations):
         dd = dict(d, means3D=means3D.detach(), sh=sh.detach(), opacities=opacities.detach(), scales=scales.detach(),
                   rotations=rotations.detach())
         f = ref.forward(dd, internals=False, sync=False)
         ctx.ref = ref
-        return f["color"]
+        ctx.mark_non_differentiable(f["radii"])
+        return f["color"], f["radii"]
 
     @staticmethod
-    def backward(ctx, g):
+    def backward(ctx, g, _g_radii):
         r = ctx.ref.backward(g.contiguous(), sync=False)
-        return None, None, r["means3D"], r["sh"], r["opacity"], r["scales"], r["rot"]
+        return None, None, r["means3D"], r["means2D"], r["sh"], r["opacity"], r["scales"], r["rot"]
 
 
 def main():
@@ -85,32 +90,41 @@ def main():
         groups = [{"params": [p[k]], "lr": lr, "name": k} for k, lr in
                   (("xyz", 1.6e-4), ("f_dc", 2.5e-3), ("f_rest", 1.25e-4), ("opacity", 0.05), ("scaling", 5e-3),
                    ("rotation", 1e-3))]
-        opt = (FusedAdam if kind in ("+adam", "+split", "+act") else torch.optim.Adam)(groups, lr=0.0, eps=1e-15)
+        opt = (FusedAdam if kind in FUSED[2:] else torch.optim.Adam)(groups, lr=0.0, eps=1e-15)
+        stats = [torch.zeros(P, device="cuda"), torch.zeros(P, 1, device="cuda"), torch.zeros(P, 1, device="cuda")]
 
         def it():
-            sh = (p["f_dc"], p["f_rest"]) if kind in ("+split", "+act") else torch.cat((p["f_dc"], p["f_rest"]), dim=1)
-            if kind == "+act":
+            sh = (p["f_dc"], p["f_rest"]) if kind in FUSED[3:] else torch.cat((p["f_dc"], p["f_rest"]), dim=1)
+            if kind in FUSED[4:]:
                 opac, scl, rot = activate(p["opacity"], p["scaling"], p["rotation"])
             else:
                 opac, scl = torch.sigmoid(p["opacity"]), torch.exp(p["scaling"])
                 rot = F.normalize(p["rotation"])
+            m2 = torch.zeros_like(p["xyz"], requires_grad=True)      # screenspace_points
             if kind == "reference":
-                img = RefRaster.apply(ref, d, p["xyz"], sh, opac, scl, rot)
+                img, radii = RefRaster.apply(ref, d, p["xyz"], m2, sh, opac, scl, rot)
             else:
-                m2 = torch.zeros_like(p["xyz"], requires_grad=True)
-                img, _ = raster(means3D=p["xyz"], means2D=m2, opacities=opac, shs=sh, scales=scl, rotations=rot)
-            if kind in ("+loss", "+adam", "+split", "+act"):
+                img, radii = raster(means3D=p["xyz"], means2D=m2, opacities=opac, shs=sh, scales=scl, rotations=rot)
+            if kind in FUSED[1:]:
                 loss, _ = l1_ssim_loss(img, gt, LAMBDA)
             else:
                 loss = torch_loss(img, gt, win)
             loss.backward()
+            with torch.no_grad():                                    # train.py:113-116
+                if kind == "+stats":
+                    densification_stats(radii, m2.grad, *stats)
+                else:
+                    vis = radii > 0
+                    stats[0][vis] = torch.max(stats[0][vis], radii[vis])
+                    stats[1][vis] += torch.norm(m2.grad[vis, :2], dim=-1, keepdim=True)
+                    stats[2][vis] += 1
             opt.step()
             opt.zero_grad(set_to_none=True)
         return it
 
     if os.environ.get("GSR_TIMELINE"):
         from torch.profiler import ProfilerActivity, profile
-        it = make("+act")
+        it = make("+stats")
         for _ in range(3):
             it()
         torch.cuda.synchronize()
@@ -125,7 +139,7 @@ def main():
                 f.write("%9.1f %8.1f  %s\n" % (e.time_range.start - t0, e.time_range.end - e.time_range.start, e.name[:100]))
         return
     res = {}
-    for kind in ("reference", "raster", "+loss", "+adam", "+split", "+act"):
+    for kind in ("reference",) + FUSED:
         it = make(kind)
         for _ in range(3):
             it()
@@ -139,7 +153,7 @@ def main():
         torch.cuda.synchronize()
         res[kind] = a.elapsed_time(b) / n
         print(f"{kind:10s} {res[kind]:7.3f} ms/iteration  ({1000 / res[kind]:6.1f} it/s)", flush=True)
-    print(f"train.py-style iteration, P={P} {W}x{H}: {res['reference'] / res['+act']:.2f}x the reference stack")
+    print(f"train.py-style iteration, P={P} {W}x{H}: {res['reference'] / res['+stats']:.2f}x the reference stack")
 
 
 if __name__ == "__main__":
