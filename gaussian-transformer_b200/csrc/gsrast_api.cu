@@ -652,9 +652,23 @@ int gsr_l1_ssim_loss(int32_t C, int32_t H, int32_t W, const float* img, const fl
   loss_finish_kernel<<<1, 1, 0, stream>>>(acc, n, lambda_dssim, out3);
   if (dL_dimg) {
     loss_pass2_kernel<<<grid, LOSS_THREADS, 0, stream>>>(H, W, img, gt, maps, (float)((1.0 - lambda_dssim) / n),
-                                                    (float)(lambda_dssim / n), dL_dimg);
+                                                    (float)(lambda_dssim / n), nullptr, dL_dimg);
     GSR_STAGE("loss_pass2", 0, stream);
   }
+  return GSR_OK;
+}
+
+int gsr_l1_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img, const float* gt, float lambda_dssim,
+                         const float* upstream, const void* scratch, float* dL_dimg, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (C <= 0 || H <= 0 || W <= 0 || C > 65535) return fail(GSR_ERR_INVALID, "gsr_l1_ssim_backward: bad C / H / W");
+  if (!img || !gt || !scratch || !dL_dimg) return fail(GSR_ERR_INVALID, "gsr_l1_ssim_backward: NULL pointer");
+  const float* maps = (const float*)((const char*)scratch + align_up(LOSS_SLOTS * sizeof(LossAcc)));
+  const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
+  const double n = (double)C * H * W;
+  loss_pass2_kernel<<<grid, LOSS_THREADS, 0, stream>>>(H, W, img, gt, maps, (float)((1.0 - lambda_dssim) / n),
+                                                  (float)(lambda_dssim / n), upstream, dL_dimg);
+  GSR_STAGE("loss_pass2", 0, stream);
   return GSR_OK;
 }
 

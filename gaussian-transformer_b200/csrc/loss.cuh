@@ -181,7 +181,8 @@ __global__ void loss_finish_kernel(const LossAcc* __restrict__ acc, double n, fl
 __global__ void __launch_bounds__(LOSS_THREADS) loss_pass2_kernel(int H, int W, const float* __restrict__ img,
                                                                   const float* __restrict__ gt,
                                                                   const float* __restrict__ maps, float w_l1,
-                                                                  float w_ssim, float* __restrict__ dL_dimg) {
+                                                                  float w_ssim, const float* __restrict__ upstream,
+                                                                  float* __restrict__ dL_dimg) {
   __shared__ float s_in[3 * LE * LIS];
   __shared__ float s_mid[3 * LE * LMS];
   const int tid = threadIdx.x, ch = blockIdx.z;
@@ -201,6 +202,11 @@ __global__ void __launch_bounds__(LOSS_THREADS) loss_pass2_kernel(int H, int W, 
   float m[3][VSEG];
   filter_cols<3>(s_mid, tid, m);
   const int tx = tid & 31, ty0 = (tid >> 5) * VSEG, px = blockIdx.x * LT + tx;
+  if (upstream != nullptr) {  // d(loss)/d(img) scaled by the upstream gradient of the loss (a device scalar)
+    const float u = __ldg(upstream);
+    w_l1 *= u;
+    w_ssim *= u;
+  }
 #pragma unroll
   for (int o = 0; o < VSEG; o++) {
     const int py = blockIdx.y * LT + ty0 + o;

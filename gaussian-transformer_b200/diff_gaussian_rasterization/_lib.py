@@ -35,7 +35,7 @@ EXPORTS = (
     "gsr_version", "gsr_compiled_arch", "gsr_last_error", "gsr_scratch_bytes", "gsr_forward_pre",
     "gsr_forward_post", "gsr_backward", "gsr_mark_visible", "gsr_get_views", "gsr_profile_enable", "gsr_profile_read",
     "gsr_sh_color_factors", "gsr_sh_grad_from_factors", "gsr_knn_scratch_bytes", "gsr_knn_dist2",
-    "gsr_loss_scratch_bytes", "gsr_l1_ssim_loss",
+    "gsr_loss_scratch_bytes", "gsr_l1_ssim_loss", "gsr_l1_ssim_backward",
     "gsr_backward_blend", "gsr_backward_geometry", "gsr_backward_sh_factors",
     "gsr_adam_step", "gsr_forward", "gsr_backward_geometry_split",
     "gsr_activate", "gsr_activate_backward", "gsr_densification_stats",
@@ -71,6 +71,7 @@ def load(path=LIB_PATH):
     lib.gsr_mark_visible.argtypes = [i32, vp, vp, vp, vp, vp]
     lib.gsr_loss_scratch_bytes.argtypes = [i32, i32, i32, szp]
     lib.gsr_l1_ssim_loss.argtypes = [i32, i32, i32, vp, vp, ctypes.c_float, vp, vp, vp, vp]
+    lib.gsr_l1_ssim_backward.argtypes = [i32, i32, i32, vp, vp, ctypes.c_float, vp, vp, vp, vp]
     lib.gsr_knn_scratch_bytes.argtypes = [i32, szp]
     lib.gsr_knn_dist2.argtypes = [i32, vp, vp, vp, vp]
     lib.gsr_sh_color_factors.argtypes = [i32, vp, vp, vp, vp]

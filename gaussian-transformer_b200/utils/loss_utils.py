@@ -26,40 +26,48 @@ def _check(img, gt):
         raise RuntimeError("loss_utils: the second image is the ground truth and gets no gradient")
 
 
-def _launch(img, gt, lam, want_grad):
-    """img, gt: contiguous float32 (C,H,W).  Returns (out3 tensor [L1, SSIM, loss], d loss / d img or None)."""
+def _forward(img, gt, lam):
+    """img, gt: contiguous float32 (C,H,W).  Returns (out3 tensor [L1, SSIM, loss], scratch holding the derivative
+    maps for the gradient pass)."""
     C, H, W = img.shape
     dev = img.device
     out3 = torch.empty(3, dtype=torch.float32, device=dev)
-    grad = torch.empty_like(img) if want_grad else None
     with torch.cuda.device(dev):
         nbytes = ctypes.c_size_t()
         _lib.check(_lib.lib.gsr_loss_scratch_bytes(C, H, W, ctypes.byref(nbytes)))
         scratch = torch.empty(nbytes.value, dtype=torch.uint8, device=dev)
-        _lib.check(_lib.lib.gsr_l1_ssim_loss(C, H, W, img.data_ptr(), gt.data_ptr(), float(lam), out3.data_ptr(),
-                                             grad.data_ptr() if want_grad else None, scratch.data_ptr(),
-                                             torch.cuda.current_stream(dev).cuda_stream))
-    return out3, grad
+        _lib.check(_lib.lib.gsr_l1_ssim_loss(C, H, W, img.data_ptr(), gt.data_ptr(), float(lam), out3.data_ptr(), None,
+                                             scratch.data_ptr(), torch.cuda.current_stream(dev).cuda_stream))
+    return out3, scratch
 
 
 class _L1SSIM(torch.autograd.Function):
-    """out3 = [L1, SSIM, (1-l)*L1 + l*(1-SSIM)]; only out3[2] carries a gradient (the others are reports)."""
+    """out3 = [L1, SSIM, (1-l)*L1 + l*(1-SSIM)]; only out3[2] carries a gradient (the others are reports).  The
+    gradient pass runs in backward, scaled by the upstream gradient read on the device (no extra multiply)."""
 
     @staticmethod
     def forward(ctx, img, gt, lam):
         x = img.detach().to(torch.float32).contiguous()
         y = gt.detach().to(torch.float32).contiguous()
-        shape = x.shape
+        ctx.shape = x.shape
         if x.dim() == 4:  # the mean over everything is the same with batch folded into channels
-            x, y = x.reshape(-1, *shape[2:]), y.reshape(-1, *shape[2:])
-        out3, grad = _launch(x, y, lam, ctx.needs_input_grad[0])
-        ctx.save_for_backward(grad.reshape(shape) if grad is not None else None)
+            x, y = x.reshape(-1, *x.shape[2:]), y.reshape(-1, *y.shape[2:])
+        out3, scratch = _forward(x, y, lam)
+        ctx.lam = lam
+        ctx.save_for_backward(x, y, scratch)
         return out3
 
     @staticmethod
     def backward(ctx, g_out):
-        (grad,) = ctx.saved_tensors
-        return (grad * g_out[2] if grad is not None else None), None, None
+        x, y, scratch = ctx.saved_tensors
+        C, H, W = x.shape
+        up = g_out.to(torch.float32).contiguous()[2:3]
+        grad = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib.gsr_l1_ssim_backward(C, H, W, x.data_ptr(), y.data_ptr(), float(ctx.lam), up.data_ptr(),
+                                                     scratch.data_ptr(), grad.data_ptr(),
+                                                     torch.cuda.current_stream(x.device).cuda_stream))
+        return grad.reshape(ctx.shape), None, None
 
 
 def l1_ssim_loss(image, gt_image, lambda_dssim=0.2):

@@ -212,6 +212,12 @@ GSR_API int gsr_knn_dist2(int32_t P, const float* points, float* mean_dist2, voi
 GSR_API int gsr_loss_scratch_bytes(int32_t C, int32_t H, int32_t W, size_t* bytes);
 GSR_API int gsr_l1_ssim_loss(int32_t C, int32_t H, int32_t W, const float* img, const float* gt,
                              float lambda_dssim, float* out3, float* dL_dimg, void* scratch, void* stream);
+/* The gradient pass on its own, for autograd: after gsr_l1_ssim_loss(..., dL_dimg = NULL, scratch, ...) on the same
+ * img / gt / lambda, writes dL_dimg = (*upstream) * d loss / d img; `upstream` is a DEVICE float (NULL = 1) and
+ * `scratch` the untouched scratch of that forward call. */
+GSR_API int gsr_l1_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img, const float* gt,
+                                 float lambda_dssim, const float* upstream, const void* scratch, float* dL_dimg,
+                                 void* stream);
 
 /* The parameter activations in front of the rasterizer, one pass per direction over 32 B per Gaussian: replaces
  * get_opacity = sigmoid(_opacity), get_scaling = exp(_scaling), get_rotation = normalize(_rotation)

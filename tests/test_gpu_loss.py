@@ -86,7 +86,8 @@ def test_identical_images_and_upstream_scale():
     img2.grad = None
     l_b, _ = l1_ssim_loss(img2, gt, 0.2)
     l_b.backward()
-    torch.testing.assert_close(g3, 3.0 * img2.grad, rtol=1e-6, atol=0)
+    # the upstream scale enters the two weights before they are combined: one rounding of the larger term
+    torch.testing.assert_close(g3, 3.0 * img2.grad, rtol=1e-6, atol=1e-6 * g3.abs().max().item())
 
 
 def test_errors():

@@ -49,6 +49,18 @@ def main():
         img.grad = None
         torch_loss(img[None], gt[None], win, 0.2).backward()
 
+    if os.environ.get("GSR_TIMELINE"):
+        from torch.profiler import ProfilerActivity, profile
+        for _ in range(3):
+            ours()
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA]) as tp:
+            ours(); ours()
+            torch.cuda.synchronize()
+        ev = sorted((e for e in tp.events() if e.device_type.name == "CUDA"), key=lambda e: e.time_range.start)
+        for e in ev:
+            print("%9.1f %8.1f  %s" % (e.time_range.start - ev[0].time_range.start, e.time_range.end - e.time_range.start, e.name[:80]))
+        return
     t_o, t_r = timed(ours), timed(ref)
     px = 3 * H * W
     # algorithmic bytes: pass 1 reads img, gt and writes 3 maps; pass 2 reads 3 maps, img, gt and writes the gradient
