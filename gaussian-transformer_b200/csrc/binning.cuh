@@ -39,7 +39,7 @@ constexpr int BAND_TILES_MAX = 2048;   // cursor-table entries per warp (8 KB)
 constexpr int BAND_ROWS = GSR_BAND_ROWS;  // tile rows per band
 
 struct BinPlan {
-  int chunk;       // Gaussians per chunk (a power of two >= 1024)
+  int chunk;       // Gaussians per chunk (a power of two >= 128)
   int chunk_shift; // log2(chunk)
   int n_chunks;
   int rows_per_band, n_bands, band_tiles;
@@ -47,8 +47,7 @@ struct BinPlan {
 
 inline BinPlan make_bin_plan(int P, int gx, int gy) {
   BinPlan p;
-  int shift = 10;                          // at least 1024 Gaussians per chunk ...
-  while (((long long)1 << shift) * 1024 < P) shift++;  // ... and at most 1024 chunks
+  const int shift = bin_chunk_shift((size_t)P, (size_t)gx * gy);  // common.cuh (also sizes the count matrix)
   const int chunk = 1 << shift;
   p.chunk_shift = shift;
   p.chunk = chunk;
