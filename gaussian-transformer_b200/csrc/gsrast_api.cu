@@ -14,6 +14,8 @@
 #include "binning.cuh"
 #include "common.cuh"
 #include "depth_sort.cuh"
+#include <cstdlib>
+
 #include "knn.cuh"
 #include "loss.cuh"
 #include "adam.cuh"
@@ -339,11 +341,23 @@ int forward_post_impl(const gsr_inputs* in, const void* geom, void* binning, voi
       // order-preserving walk; when the parallel count ran it left the clipped rectangles in depth order
       const int tasks = plan.n_chunks * plan.n_bands;
       const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
-      GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
-               "bin_pass smem attribute");
-      bin_pass_kernel<true><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
-          in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list,
-          bin_parallel(T, plan) ? g.rects : nullptr, guard, cap);
+      // lists that outgrow the L2 (or chunks with long serial walks) take the CTA-cooperative, band-major kernel
+      const char* force = getenv("GSR_BIN_CTA");  // dev / test switch: "0" / "1"
+      const bool long_lists = (size_t)R * 4 > ((size_t)64 << 20) || plan.chunk > 1024;
+      const bool cta = plan.chunk >= 256 && (force ? force[0] == '1' : long_lists);
+      if (cta) {
+        GSR_CUDA(cudaFuncSetAttribute(bin_scatter_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
+                 "bin_scatter smem attribute");
+        bin_scatter_cta_kernel<<<tasks, BIN_WARPS * 32, bin_smem, stream>>>(
+            in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list,
+            bin_parallel(T, plan) ? g.rects : nullptr, guard, cap);
+      } else {
+        GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
+                 "bin_pass smem attribute");
+        bin_pass_kernel<true><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
+            in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list,
+            bin_parallel(T, plan) ? g.rects : nullptr, guard, cap);
+      }
       GSR_STAGE("bin_scatter", in->debug, stream);
     }
   }

@@ -160,6 +160,25 @@ def test_dp_step_factored_two_views_one_rank():
         assert rel_err(np_(out[k]).reshape(want.shape), np_(want)) <= 1e-3, k
 
 
+def test_cta_scatter_kernel_writes_the_same_lists(monkeypatch):
+    """bin_scatter_cta_kernel (taken automatically once point_list outgrows the L2) against bin_pass<true>: identical
+    per-tile lists, image and n_contrib."""
+    from diff_gaussian_rasterization import _C
+    sc = S.scene_S(80000, 640, 360, seed=9, M=16, sh_degree=3)
+    d = to_device(sc)
+    e = torch.Tensor([])
+    res = []
+    for force in ("0", "1"):
+        monkeypatch.setenv("GSR_BIN_CTA", force)
+        res.append(_C.rasterize_gaussians(d["bg"], d["means3D"], e, d["opacities"], d["scales"], d["rotations"], 1.0, e,
+                                          d["viewmatrix"], d["projmatrix"], d["tanfovx"], d["tanfovy"], sc["H"],
+                                          sc["W"], d["sh"], 3, d["campos"], False, False))
+    (R0, c0, _, _, b0, i0), (R1, c1, _, _, b1, i1) = res
+    N = sc["W"] * sc["H"]
+    assert R0 == R1 and R0 > 100000
+    assert torch.equal(b0[:4 * R0], b1[:4 * R0]) and torch.equal(c0, c1) and torch.equal(i0[:8 * N], i1[:8 * N])
+
+
 def test_speculative_forward_hit_miss_and_overflow_guard():
     """gsr_forward launches phase 2 before num_rendered reaches the host, against a buffer sized from a hint: a
     hit, a miss (hint far too small: the device-side guard must keep the kernels from touching the short buffer)
