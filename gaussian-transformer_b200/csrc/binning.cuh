@@ -216,15 +216,26 @@ constexpr size_t BINC_SMEM_MAX = 200 * 1024;
 #ifndef GSR_BINC_BANDS
 #define GSR_BINC_BANDS 1
 #endif
-constexpr int BINC_BANDS = GSR_BINC_BANDS;  // bands of tile rows per chunk in the parallel kernels
+constexpr int BINC_BANDS = GSR_BINC_BANDS;  // minimum number of bands of tile rows per chunk
+constexpr size_t BINC_TABLE_TARGET = 48 * 1024;  // per-CTA table size that still lets ~4 CTAs share an SM
 
-// the shared-memory table must fit (tile coordinates always fit the 16-bit rectangle fields: W, H < 2^20)
-inline bool bin_parallel(size_t T, const BinPlan& plan) {
-  return 4 * T <= BINC_BANDS * BINC_SMEM_MAX && plan.n_bands > 0;
+// Bands of tile rows per chunk in bin_count_cta_kernel (its blockIdx.y): 1 while the table of all tiles is small
+// (1080p: 32 KB); larger grids are cut so that several CTAs fit an SM (3840x2160: 130 KB -> 3 bands of 43 KB; one
+// 130 KB table per SM left 8 warps per SM for 228 M shared-memory atomics, 0.68 ms).
+inline int binc_bands(int gx, int gy) {
+  const size_t bytes = (size_t)4 * gx * gy;
+  int bands = (int)((bytes + BINC_TABLE_TARGET - 1) / BINC_TABLE_TARGET);
+  if (bands < BINC_BANDS) bands = BINC_BANDS;
+  if (bands > gy) bands = gy;
+  return bands < 1 ? 1 : bands;
 }
 inline size_t binc_smem(int gx, int gy) {  // table of one band
-  const int rows = (gy + BINC_BANDS - 1) / BINC_BANDS;
+  const int bands = binc_bands(gx, gy), rows = (gy + bands - 1) / bands;
   return (size_t)4 * rows * gx;
+}
+// the shared-memory table must fit (tile coordinates always fit the 16-bit rectangle fields: W, H < 2^20)
+inline bool bin_parallel(int gx, int gy, const BinPlan& plan) {
+  return binc_smem(gx, gy) <= BINC_SMEM_MAX && binc_bands(gx, gy) <= 65535 && plan.n_bands > 0;
 }
 
 __device__ __forceinline__ uint2 pack_rect(int minx, int miny, int maxx, int maxy) {

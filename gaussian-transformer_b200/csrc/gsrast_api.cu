@@ -281,12 +281,12 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   }
   {
   ScopedStage prof_(GSR_STAGE_BIN_COUNT, stream);
-  if (bin_parallel(T, plan)) {
+  if (bin_parallel(cam.gx, cam.gy, plan)) {
     // parallel binning, counting half: one CTA per chunk, all tiles in shared memory
     const size_t smem = binc_smem(cam.gx, cam.gy);
     GSR_CUDA(cudaFuncSetAttribute(bin_count_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
              "bin_count smem attribute");
-    bin_count_cta_kernel<<<dim3(plan.n_chunks, BINC_BANDS), BINC_THREADS, smem, stream>>>(
+    bin_count_cta_kernel<<<dim3(plan.n_chunks, binc_bands(cam.gx, cam.gy)), BINC_THREADS, smem, stream>>>(
         in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan.chunk, g.rects, im.matrix);
   } else {
     // order-preserving serial walk (tile grids too large for a shared-memory table), counting half
@@ -350,13 +350,13 @@ int forward_post_impl(const gsr_inputs* in, const void* geom, void* binning, voi
                  "bin_scatter smem attribute");
         bin_scatter_cta_kernel<<<tasks, BIN_WARPS * 32, bin_smem, stream>>>(
             in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list,
-            bin_parallel(T, plan) ? g.rects : nullptr, guard, cap);
+            bin_parallel(cam.gx, cam.gy, plan) ? g.rects : nullptr, guard, cap);
       } else {
         GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
                  "bin_pass smem attribute");
         bin_pass_kernel<true><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
             in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list,
-            bin_parallel(T, plan) ? g.rects : nullptr, guard, cap);
+            bin_parallel(cam.gx, cam.gy, plan) ? g.rects : nullptr, guard, cap);
       }
       GSR_STAGE("bin_scatter", in->debug, stream);
     }
