@@ -42,6 +42,7 @@ struct BinPlan {
   int chunk;       // Gaussians per chunk (a power of two >= 128)
   int chunk_shift; // log2(chunk)
   int n_chunks;
+  int band_major;  // task order of bin_pass_kernel: 1 = all chunks of band 0 first (keeps the lists being written small)
   int rows_per_band, n_bands, band_tiles;
 };
 
@@ -52,6 +53,7 @@ inline BinPlan make_bin_plan(int P, int gx, int gy) {
   p.chunk_shift = shift;
   p.chunk = chunk;
   p.n_chunks = P > 0 ? (P + chunk - 1) / chunk : 0;
+  p.band_major = 1;  // measured at 1 M Gaussians / 1080p: 151 -> 135 us for the scatter walk
   p.rows_per_band = BAND_TILES_MAX / gx;
   if (p.rows_per_band < 1) p.rows_per_band = 0;  // image wider than 32768 px: unsupported, caller reports it
   // (measured at 1M Gaussians / 1080p with the rectangles precomputed: 4, 8, 17 tile rows per band give 148, 149,
@@ -146,7 +148,9 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_pass_kernel(int P, const u
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const int task = blockIdx.x * BIN_WARPS + w;
   if (task >= plan.n_chunks * plan.n_bands) return;
-  const int chunk = task / plan.n_bands, band = task - chunk * plan.n_bands;
+  int chunk, band;
+  if (plan.band_major) { band = task / plan.n_chunks; chunk = task - band * plan.n_chunks; }
+  else { chunk = task / plan.n_bands; band = task - chunk * plan.n_bands; }
   const int by0 = band * plan.rows_per_band, by1 = min(gy, by0 + plan.rows_per_band);
   const int ntab = (by1 - by0) * gx;
   const int tile0 = by0 * gx;
