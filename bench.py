@@ -114,9 +114,9 @@ def algorithmic_bytes(P, V, R, N, K, M):
 # summarised in profiles/r01_ncu_full_metrics.txt (a property of the workload, not of the run: bench.py only ever
 # runs C2).  Below the algorithmic bytes wherever list entries and per-Gaussian records are re-read from the L2.
 NCU_DRAM_BYTES_C2 = {
-    "preprocess_fwd": 216.99e6 + 41.03e6,
-    "render_fwd": 65.69e6 + 18.70e6,
-    "render_bwd": 117.35e6 + 6.70e6,
+    "preprocess_fwd": 217.00e6 + 40.97e6,
+    "render_fwd": 65.70e6 + 18.59e6,
+    "render_bwd": 117.31e6 + 6.87e6,
     "preprocess_bwd": 285.00e6 + 242.47e6,
 }
 
