@@ -233,7 +233,7 @@ def test_split_sh_matches_concatenated(P, M, deg):
     assert float(a[2].abs().max()) > 0 and (deg == 0 or float(a[3].abs().max()) > 0)
     for x, y in zip(a[2:], b[2:]):
         assert x.shape == y.shape
-        assert rel_err(np_(y), np_(x)) <= 1e-4  # order of the blend atomics only
+        assert rel_err(np_(y), np_(x)) <= 1e-3  # order of the blend atomics only (same bar as the parity tests)
 
 
 def test_colors_and_cov_paths():
