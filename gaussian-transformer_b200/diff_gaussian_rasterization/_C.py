@@ -72,7 +72,7 @@ def _check_means(means3D):
         raise RuntimeError("gsrast: means3D must be a CUDA tensor (there is no CPU path)")
 
 
-_r_hint = {}  # device index -> largest num_rendered seen (sizes the speculative binning buffer)
+_r_hint = {}  # (device index, P, W, H) -> recent num_rendered (sizes the speculative binning buffer)
 
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
@@ -104,10 +104,11 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         out_color = torch.empty(3, H, W, dtype=torch.float32, device=dev)
         host = _host_result()
         stream = torch.cuda.current_stream(dev)
-        # Phase 2 is launched speculatively against a binning buffer sized from the largest num_rendered seen so far
-        # on this device (+25 %), so the GPU does not idle during the one host round trip (rasterizer_impl.cu:281);
+        # Phase 2 is launched speculatively against a binning buffer sized from the num_rendered this scene size
+        # produced recently on this device (+25 %), so the GPU does not idle during the one host round trip (rasterizer_impl.cu:281);
         # a miss (first call, or a much denser view) falls back to allocate-then-launch.
-        hint = _r_hint.get(dev.index, 0)
+        key = (dev.index, P, W, H)  # a scene of another size starts without a hint (one allocate-then-launch call)
+        hint = _r_hint.get(key, 0)
         cap = min(hint + hint // 4 + 65536, 0x7FFFFFFF) if hint > 0 else 0
         binning = torch.empty(_lib.scratch_bytes(P, cap, W, H)[1] if cap > 0 else 0, **u8)
         _lib.check(_lib.lib.gsr_forward(ctypes.byref(args), geom.data_ptr(), _ptr(binning) if cap > 0 else 0, cap,
@@ -118,7 +119,9 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
             raise RuntimeError("gsrast: point is filtered although prefiltered is set. This shouldn't happen!")
         if R > 0x7FFFFFFF:
             raise RuntimeError(f"gsrast: num_rendered = {R} does not fit a 32-bit int")
-        _r_hint[dev.index] = max(R, hint - hint // 16)  # follows shrinking scenes too (decays ~6 % per call)
+        if len(_r_hint) > 64:
+            _r_hint.clear()
+        _r_hint[key] = max(R, hint - hint // 16)  # follows shrinking scenes too (decays ~6 % per call)
         if R > cap or cap == 0:
             _, bb, _, _ = _lib.scratch_bytes(P, R, W, H)
             binning = torch.empty(bb if R > 0 else 0, **u8)

@@ -187,7 +187,7 @@ def test_speculative_forward_hit_miss_and_overflow_guard():
     sc = S.scene_S(150000, 640, 360, seed=8, M=16, sh_degree=3)
     d = to_device(sc)
     e = torch.Tensor([])
-    dev = d["means3D"].device.index
+    dev = (d["means3D"].device.index, sc["P"], sc["W"], sc["H"])
 
     def fwd():
         return _C.rasterize_gaussians(d["bg"], d["means3D"], e, d["opacities"], d["scales"], d["rotations"], 1.0, e,
