@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_scatter_cta_kernel(
 // ---------------------------------------------------------------------------------------------------------------
 // Counting needs no order, so the counting half is fully parallel whenever a table of all T tiles fits in shared
 // memory: bin_count_cta<<<chunk>>> = one CTA per chunk, every thread adds its own Gaussians' rectangles with
-// shared-memory atomics.  It also leaves each Gaussian's clipped tile rectangle in depth order (rects[k]), so the
+// shared-memory atomics (as per-row difference arrays, see the kernel).  It also leaves each Gaussian's clipped tile rectangle in depth order (rects[k]), so the
 // ordered scatter walk (bin_pass<true>) reads 8 coalesced bytes per Gaussian instead of gathering g0 again.
 // (Measured alternative, removed: an unordered atomic scatter of sorted positions followed by a per-tile fix-up
 // that ranks the 1.4-element (chunk, tile) cells -- bit-exact, but 12 M scattered 4-byte writes + 12 M gathers cost
@@ -235,7 +235,7 @@ inline int binc_bands(int gx, int gy) {
 }
 inline size_t binc_smem(int gx, int gy) {  // table of one band
   const int bands = binc_bands(gx, gy), rows = (gy + bands - 1) / bands;
-  return (size_t)4 * rows * gx;
+  return (size_t)4 * rows * (gx + 1);  // difference array: one extra column per row
 }
 // the shared-memory table must fit (tile coordinates always fit the 16-bit rectangle fields: W, H < 2^20)
 inline bool bin_parallel(int gx, int gy, const BinPlan& plan) {
@@ -244,34 +244,6 @@ inline bool bin_parallel(int gx, int gy, const BinPlan& plan) {
 
 __device__ __forceinline__ uint2 pack_rect(int minx, int miny, int maxx, int maxy) {
   return make_uint2((uint32_t)minx | ((uint32_t)maxx << 16), (uint32_t)miny | ((uint32_t)maxy << 16));
-}
-
-// for every tile of the rect: f(tile index).  Rectangles of more than BIG tiles are spread over the warp.
-// The rectangle is clipped to tile rows [by0, by1) and f receives the index relative to row by0.
-template <class F>
-__device__ __forceinline__ void for_rect_tiles(uint2 r, int gx, int by0, int by1, int lane, F f) {
-  constexpr int BIG = 128;
-  const int minx = r.x & 0xffff, maxx = r.x >> 16;
-  const int miny = max((int)(r.y & 0xffff), by0) - by0, maxy = max(miny, min((int)(r.y >> 16), by1) - by0);
-  r.y = (uint32_t)miny | ((uint32_t)maxy << 16);
-  const int wdt = maxx - minx, nt = wdt * (maxy - miny);
-  if (nt <= BIG) {
-    for (int y = miny; y < maxy; y++) {
-#pragma unroll 4
-      for (int x = minx; x < maxx; x++) f(y * gx + x, false, 0);
-    }
-  }
-  unsigned big = __ballot_sync(0xffffffffu, nt > BIG);
-  while (big) {
-    const int src = __ffs(big) - 1;
-    big &= big - 1;
-    const uint32_t rx = __shfl_sync(0xffffffffu, r.x, src), ry = __shfl_sync(0xffffffffu, r.y, src);
-    const int x0 = rx & 0xffff, w = (int)(rx >> 16) - x0, y0 = ry & 0xffff, n = w * ((int)(ry >> 16) - y0);
-    for (int t = lane; t < n; t += 32) {
-      const int ty = t / w;
-      f((y0 + ty) * gx + x0 + (t - ty * w), true, src);
-    }
-  }
 }
 
 __global__ void __launch_bounds__(BINC_THREADS) bin_count_cta_kernel(int P, const uint32_t* __restrict__ order,
@@ -283,11 +255,11 @@ __global__ void __launch_bounds__(BINC_THREADS) bin_count_cta_kernel(int P, cons
   // blockIdx.y = band of tile rows: a chunk's work is split over several CTAs (near chunks hold many more
   // instances than far ones); every band CTA scans the chunk and keeps what reaches its rows
   const int rows = (gy + gridDim.y - 1) / gridDim.y, by0 = blockIdx.y * rows, by1 = min(gy, by0 + rows);
-  const int T = max(0, by1 - by0) * gx, tile0 = by0 * gx;
-  for (int t = tid; t < T; t += BINC_THREADS) s_tab[t] = 0u;
+  const int tile0 = by0 * gx;
+  for (int t = tid; t < max(0, by1 - by0) * (gx + 1); t += BINC_THREADS) s_tab[t] = 0u;
   __syncthreads();
   const int begin = blockIdx.x * chunk_size, end = min(P, begin + chunk_size);
-  for (int k0 = begin; k0 < end; k0 += BINC_THREADS) {  // whole warps stay together (warp-wide helper below)
+  for (int k0 = begin; k0 < end; k0 += BINC_THREADS) {
     const int k = k0 + tid;
     uint2 r = make_uint2(0u, 0u);
     if (k < end) {
@@ -300,11 +272,38 @@ __global__ void __launch_bounds__(BINC_THREADS) bin_count_cta_kernel(int P, cons
       }
       if (blockIdx.y == 0) rects[k] = r;
     }
-    for_rect_tiles(r, gx, by0, by1, lane, [&](int t, bool, int) { atomicAdd(&s_tab[t], 1u); });
+    // Difference array per tile row: +1 at the rectangle's first column, -1 behind its last one (the table has
+    // gx + 1 columns); a row prefix sum at the end turns them into per-tile counts.  2 atomics per tile row instead
+    // of one per tile, and -- lanes run in lockstep -- the loop length is the tallest rectangle of the warp in ROWS.
+    {
+      const int minx = r.x & 0xffff, maxx = r.x >> 16;
+      const int y0 = max((int)(r.y & 0xffff), by0) - by0, y1 = min((int)(r.y >> 16), by1) - by0;
+      if (maxx > minx)
+        for (int y = y0; y < y1; y++) {
+          atomicAdd(&s_tab[y * (gx + 1) + minx], 1u);
+          atomicAdd(&s_tab[y * (gx + 1) + maxx], 0xffffffffu);
+        }
+    }
   }
   __syncthreads();
-  uint32_t* row = matrix + (size_t)blockIdx.x * gx * gy + tile0;
-  for (int t = tid; t < T; t += BINC_THREADS) row[t] = s_tab[t];
+  // row prefix sums (one warp per row, 32 columns at a time with a carry) straight into matrix[chunk][tile]
+  uint32_t* out = matrix + (size_t)blockIdx.x * gx * gy + tile0;
+  const int n_rows = max(0, by1 - by0);
+  for (int y = tid >> 5; y < n_rows; y += BINC_THREADS / 32) {
+    uint32_t carry = 0;
+    for (int x0 = 0; x0 < gx; x0 += 32) {
+      const int x = x0 + lane;
+      uint32_t v = x < gx ? s_tab[y * (gx + 1) + x] : 0u;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+        if (lane >= o) v += t;
+      }
+      v += carry;
+      if (x < gx) out[y * gx + x] = v;
+      carry = __shfl_sync(0xffffffffu, v, 31);
+    }
+  }
 }
 
 // matrix[chunk][tile] -> exclusive prefix over chunks (in place); tile_count[tile] = column total.
