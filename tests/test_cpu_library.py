@@ -65,3 +65,23 @@ def test_product_never_references_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h")):
                 src = open(os.path.join(dp, f)).read()
                 assert "liboracle" not in src and "oracle/" not in src and "checkers" not in src, f
+
+
+def test_utils_package_falls_through_to_the_callers_utils(tmp_path):
+    """The reference's `utils/` has no __init__.py; this repo's `utils` (loss_utils only) must not hide its other
+    modules (`scene/__init__.py:15` imports utils.system_utils): the package path is extended along sys.path."""
+    import subprocess
+    import sys
+    (tmp_path / "utils").mkdir()
+    (tmp_path / "utils" / "system_utils.py").write_text("def searchForMaxIteration(folder):\n    return 7\n")
+    (tmp_path / "utils" / "loss_utils.py").write_text("WHO = 'caller'\n")
+    code = ("import sys; sys.path.insert(0, %r)\n"
+            "from utils.system_utils import searchForMaxIteration as f\n"
+            "import utils.loss_utils as lu\n"
+            "print(f('x'), hasattr(lu, 'l1_ssim_loss'), hasattr(lu, 'WHO'))\n") % os.path.join(ROOT, "gaussian-transformer_b200")
+    for first in (True, False):   # caller's tree first on the path (python train.py) or after this repo's package
+        env = dict(os.environ, PYTHONPATH=str(tmp_path))
+        out = subprocess.run([sys.executable, "-c", code], cwd=str(tmp_path) if first else "/", env=env,
+                             capture_output=True, text=True, timeout=120)
+        assert out.returncode == 0, out.stderr
+        assert out.stdout.split() == ["7", "True", "False"], out.stdout
