@@ -2,7 +2,8 @@
 (yaw -15 ... +15 degrees, looking at (0, 0, 6)) at 1920x1080, forward + backward of every view, per-Gaussian gradients
 summed over the batch.  STRONG scaling: the 8 views are split over G ranks (gsr_dp.shard_views), each rank renders its
 block one view after the other, then the exchange of gsr_dp.dp_step_factored (all-gather of 12 B/Gaussian/view SH
-factors + all-reduce of the 44 B/Gaussian small gradients, SH gradient rebuilt locally).  G = 1 has no exchange.
+factors + all-reduce of the 44 B/Gaussian small gradients, SH gradient rebuilt locally).  G = 1 has no exchange but
+sums the batch the same way (factors kept, one rebuild); --full-sum accumulates full gradients instead.
 
   python tools/c3_bench.py                                                     # 1 GPU
   python -m torch.distributed.run --nnodes=1 --nproc-per-node G --master-addr 127.0.0.1 tools/c3_bench.py
@@ -34,6 +35,7 @@ def main():
     ap.add_argument("--views", type=int, default=8)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--full-sum", action="store_true", help="1 GPU: sum full gradients instead of SH factors")
     args = ap.parse_args()
     rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
     dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", 0)))
@@ -63,7 +65,8 @@ def main():
         rendered.append(radii)
         return {k: leaves[k].grad for k in LEAVES}
 
-    if world == 1:
+    if args.full_sum:
+        # plain accumulation of the full 236 B/Gaussian gradients (what dp_step does), single GPU only
         flat = gsr_dp.FlatGrads({k: tuple(t[k].shape) for k in LEAVES}, dev)
 
         def step():
@@ -74,6 +77,8 @@ def main():
                 flat.add_(g)
             return flat.views
     else:
+        # factored sum at every G (at G = 1 the "exchange" is local: the factors of the 8 views are kept and dL/dsh is
+        # rebuilt once per step instead of 7 read-modify-write passes over 192 B/Gaussian)
         flat = gsr_dp.FlatGrads({k: tuple(t[k].shape) for k in gsr_dp.SMALL_LEAVES}, dev)
         per_rank = (args.views + world - 1) // world
         exchange = gsr_dp.FactorExchange(per_rank, args.P, dev, world)
@@ -114,6 +119,7 @@ def main():
             "ms_per_step": round(1e3 * sec / args.steps, 3), "views_per_s": round(vps, 1),
             "gaussians_per_s": round(args.P * vps), "grad_abs_sum": checksum,
             "visible_last_view": int((rendered[-1] > 0).sum()),
+            "sum": "full gradients" if args.full_sum else "SH factors + rebuild",
             "exchange": "none" if world == 1 else "all-gather 12 B/Gaussian/view + all-reduce 44 B/Gaussian"}))
     if world > 1:
         dist.destroy_process_group()
