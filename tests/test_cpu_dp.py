@@ -140,6 +140,24 @@ def test_factor_exchange_world2_matches_plain_sum(tmp_path):
         np.testing.assert_allclose(got, ref, rtol=2e-4, atol=1e-6 * np.abs(ref).max())
 
 
+def test_factored_sum_without_a_process_group_matches_plain_sum():
+    """world = 1, torch.distributed not initialised (tools/c3_bench.py on one GPU): the factors of the batch's views
+    are kept locally and rebuilt once; same result as accumulating the full gradients."""
+    from checkers import Oracle
+    orc = Oracle()
+    want = gsr_dp.FlatGrads(_shapes(), "cpu")
+    gsr_dp.dp_step(lambda v: _view_grads(orc, v), N_VIEWS, want, 0, 1)
+    flat = gsr_dp.FlatGrads({k: v for k, v in _shapes().items() if k in gsr_dp.SMALL_LEAVES}, "cpu")
+    means = torch.from_numpy(S.scene_S(P, W, H, seed=11, M=M, sh_degree=DEG)["means3D"])
+    assert not dist.is_initialized()
+    for step in range(2):
+        out = gsr_dp.dp_step_factored(lambda v, e: _view_grads_factored(orc, v, e), N_VIEWS, flat, 0, 1, means, DEG,
+                                      M, rebuild=_rebuild_numpy)
+    got = torch.cat([out[k].reshape(-1) for k in gsr_dp.LEAVES]).numpy()
+    ref = want.flat.numpy()
+    np.testing.assert_allclose(got, ref, rtol=2e-4, atol=1e-6 * np.abs(ref).max())
+
+
 def test_rank_without_views_contributes_zeros():
     flat = gsr_dp.FlatGrads(_shapes(), "cpu")
     flat.flat.fill_(7.0)
