@@ -92,8 +92,12 @@ def main():
     ap.add_argument("--iterations", type=int, default=3000)
     ap.add_argument("--work", default=os.path.join(ROOT, "gpurun_out", "c4"))
     ap.add_argument("--dataset-only", action="store_true", help="write the dataset (CPU) and stop")
+    ap.add_argument("--profile", default=None, help="dev: run under torch.profiler and write the kernel / CPU-op tables "
+                                                    "to this file (the timing of such a run is not a result)")
     args = ap.parse_args()
     ref_root = os.path.abspath(args.ref_root)
+    if args.profile:
+        args.profile = os.path.abspath(args.profile)
     if not os.path.isfile(os.path.join(ref_root, "train.py")):
         sys.exit("no train.py under --ref-root %s" % ref_root)
 
@@ -133,7 +137,18 @@ def main():
     sys.argv = ["train.py", "-s", ds, "-m", out, "--iterations", str(args.iterations), "--test_iterations", "-1",
                 "--save_iterations", str(args.iterations), "--quiet"]
     os.chdir(ref_root)
-    runpy.run_path(os.path.join(ref_root, "train.py"), run_name="__main__")
+    if args.profile:
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CPU, ProfilerActivity.CUDA]) as tp:
+            runpy.run_path(os.path.join(ref_root, "train.py"), run_name="__main__")
+        ka = tp.key_averages()
+        with open(args.profile, "w") as f:
+            f.write("# %s stack, %d iterations of train.py under torch.profiler\n" % (args.stack, args.iterations))
+            f.write(ka.table(sort_by="cuda_time_total", row_limit=45, max_name_column_width=70))
+            f.write("\n")
+            f.write(ka.table(sort_by="self_cpu_time_total", row_limit=30, max_name_column_width=70))
+    else:
+        runpy.run_path(os.path.join(ref_root, "train.py"), run_name="__main__")
     torch.cuda.synchronize()
     sec = time.perf_counter() - marks["t0"]
     sys.stdout = sys.__stdout__                        # safe_state(--quiet) replaced it
