@@ -11,8 +11,15 @@ import os
 import sys
 
 _here = os.path.dirname(os.path.abspath(__file__))
+try:
+    _cwd = os.getcwd()
+except OSError:  # the working directory was removed under the process
+    _cwd = None
+_cand = None
 for _root in [""] + list(sys.path):
-    _cand = os.path.abspath(os.path.join(_root or os.getcwd(), "utils"))
+    if not (_root or _cwd):
+        continue
+    _cand = os.path.abspath(os.path.join(_root or _cwd, "utils"))
     if _cand != _here and os.path.isdir(_cand) and _cand not in __path__:
         __path__.append(_cand)
-del _root, _cand
+del _root, _cand, _cwd
