@@ -14,14 +14,16 @@ make, with plyfile's names, argument meaning and error types:
 Files are the PLY 1.0 format: an ASCII header (`ply`, `format`, `comment`, `element <name> <count>`, `property <type>
 <name>`, `end_header`) followed by the elements in order, as text or as packed little/big-endian records.  Written files
 use plyfile's defaults (binary, native byte order, type names `float`/`uchar`/...), so that a file saved through this
-shim is byte-identical to the one the real package writes for the same array.  List properties (faces) do not occur on
-this path (both call sites read and write one `vertex` element of scalars) and are rejected with a clear error.
+shim is byte-identical to the one the real package writes for the same array.  List properties (`property list uchar int
+vertex_indices`, the faces of a mesh) do not occur on this path -- both call sites read and write one `vertex` element of
+scalars -- but are read and written too (object columns of numpy arrays, row by row), so that a mesh PLY handed to
+`fetchPly` loads its vertices instead of failing.
 """
 import sys
 
 import numpy as np
 
-__all__ = ["PlyData", "PlyElement", "PlyProperty", "PlyParseError", "PlyHeaderParseError", "PlyElementParseError"]
+__all__ = ["PlyData", "PlyElement", "PlyProperty", "PlyListProperty", "PlyParseError", "PlyHeaderParseError", "PlyElementParseError"]
 
 # PLY type name -> numpy kind+size.  Both the classic names and the sized aliases are legal in headers.
 _TYPES = {
@@ -82,6 +84,31 @@ class PlyProperty:
         return "PlyProperty(%r, %r)" % (self._name, _NAMES[self._val_dtype])
 
 
+class PlyListProperty(PlyProperty):
+    """A variable-length property: a count of type `len_dtype` followed by that many `val_dtype` values per row."""
+
+    def __init__(self, name, len_dtype, val_dtype):
+        super().__init__(name, val_dtype)
+        code = _TYPES.get(len_dtype, len_dtype)
+        if code not in _NAMES or code[0] == "f":
+            raise ValueError("list length type %r must be an integer type" % (len_dtype,))
+        self._len_dtype = code
+
+    len_dtype = property(lambda self: self._len_dtype)
+
+    def dtype(self, byte_order="="):
+        return "|O"
+
+    def list_dtype(self, byte_order="="):
+        return np.dtype(byte_order + self._len_dtype), np.dtype(byte_order + self._val_dtype)
+
+    def __str__(self):
+        return "property list %s %s %s" % (_NAMES[self._len_dtype], _NAMES[self._val_dtype], self._name)
+
+    def __repr__(self):
+        return "PlyListProperty(%r, %r, %r)" % (self._name, _NAMES[self._len_dtype], _NAMES[self._val_dtype])
+
+
 class PlyElement:
     """A named table: `.name`, `.count`, `.properties`, `.data` (1-D structured numpy array); `el['x']` is a column."""
 
@@ -133,8 +160,12 @@ class PlyElement:
                 raise ValueError("nested records not supported")
             if not field[0]:
                 raise ValueError("field with empty name")
-            if len(field) != 2 or field[1][1] == "O":
-                raise NotImplementedError("list / multi-valued property %r: not on this path" % (field[0],))
+            if len(field) != 2:
+                raise NotImplementedError("multi-valued field %r: use an object column of arrays" % (field[0],))
+            if field[1][1] == "O":
+                props.append(PlyListProperty(field[0], (len_types or {}).get(field[0], "u1"),
+                                             (val_types or {}).get(field[0], "i4")))
+                continue
             code = field[1][1:]
             if code not in _NAMES:
                 raise ValueError("unsupported field type %r of %r" % (field[1], field[0]))
@@ -171,7 +202,9 @@ class PlyElement:
     # --- body I/O ---------------------------------------------------------------------------------------------------
     def _read(self, stream, text, byte_order):
         dt = self.dtype(byte_order)
-        if text:
+        if any(isinstance(p, PlyListProperty) for p in self._properties):
+            self._data = self._read_rows(stream, text, byte_order, dt)
+        elif text:
             self._data = self._read_txt(stream, dt)
         else:
             need = dt.itemsize * self._count
@@ -199,8 +232,71 @@ class PlyElement:
                 raise PlyElementParseError("malformed input", self, row)
         return out
 
+    def _read_rows(self, stream, text, byte_order, dt):
+        """Row-by-row reader for elements with list properties."""
+        out = np.empty(self._count, dtype=dt)
+        for row in range(self._count):
+            if text:
+                line = stream.readline()
+                if not line:
+                    raise PlyElementParseError("early end-of-file", self, row)
+                fields = iter(line.decode("ascii").split())
+            for p in self._properties:
+                try:
+                    if isinstance(p, PlyListProperty):
+                        lt, vt = p.list_dtype(byte_order)
+                        if text:
+                            n = int(next(fields))
+                            out[p.name][row] = np.array([next(fields) for _ in range(n)], dtype=np.float64).astype(vt)
+                        else:
+                            raw = stream.read(lt.itemsize)
+                            if len(raw) < lt.itemsize:
+                                raise PlyElementParseError("early end-of-file", self, row, p)
+                            n = int(np.frombuffer(raw, lt)[0])
+                            raw = stream.read(n * vt.itemsize)
+                            if len(raw) < n * vt.itemsize:
+                                raise PlyElementParseError("early end-of-file", self, row, p)
+                            out[p.name][row] = np.frombuffer(raw, vt).astype(vt.newbyteorder("="))
+                    elif text:
+                        f = next(fields)
+                        out[p.name][row] = int(f) if p.val_dtype[0] in "iu" else float(f)
+                    else:
+                        vt = np.dtype(p.dtype(byte_order))
+                        raw = stream.read(vt.itemsize)
+                        if len(raw) < vt.itemsize:
+                            raise PlyElementParseError("early end-of-file", self, row, p)
+                        out[p.name][row] = np.frombuffer(raw, vt)[0]
+                except StopIteration:
+                    raise PlyElementParseError("early end-of-line", self, row, p)
+                except ValueError:
+                    raise PlyElementParseError("malformed input", self, row, p)
+            if text and next(fields, None) is not None:
+                raise PlyElementParseError("expected end-of-line", self, row)
+        return out
+
+    def _write_rows(self, stream, text, byte_order):
+        for rec in self._data:
+            parts = []
+            for p in self._properties:
+                v = rec[p.name]
+                if isinstance(p, PlyListProperty):
+                    lt, vt = p.list_dtype(byte_order)
+                    v = np.asarray(v)
+                    if text:
+                        parts.append("%d" % v.size)
+                        parts += [repr(float(x)) if vt.kind == "f" else "%d" % x for x in v.ravel()]
+                    else:
+                        parts.append(np.array([v.size], lt).tobytes() + v.astype(vt).tobytes())
+                elif text:
+                    parts.append(repr(float(v)) if p.val_dtype[0] == "f" else "%d" % v)
+                else:
+                    parts.append(np.array([v], np.dtype(p.dtype(byte_order))).tobytes())
+            stream.write((" ".join(parts) + "\n").encode("ascii") if text else b"".join(parts))
+
     def _write(self, stream, text, byte_order):
-        if text:
+        if any(isinstance(p, PlyListProperty) for p in self._properties):
+            self._write_rows(stream, text, byte_order)
+        elif text:
             for rec in self._data:
                 fields = []
                 for p in self._properties:
@@ -314,8 +410,15 @@ class PlyData:
                     raise PlyHeaderParseError("property without element", n)
                 f = rest.split()
                 if f and f[0] == "list":
-                    raise PlyHeaderParseError("list properties are not supported by this shim (not on the "
-                                              "Gaussian-splatting path)", n)
+                    if len(f) != 4:
+                        raise PlyHeaderParseError("expected 'property list <len type> <type> <name>'", n)
+                    if f[1] not in _TYPES or f[2] not in _TYPES:
+                        raise PlyHeaderParseError("unknown data type in %r" % rest, n)
+                    try:
+                        specs[-1][2].append(PlyListProperty(f[3], f[1], f[2]))
+                    except ValueError as e:
+                        raise PlyHeaderParseError(str(e), n)
+                    continue
                 if len(f) != 2:
                     raise PlyHeaderParseError("expected 'property <type> <name>'", n)
                 if f[0] not in _TYPES:

@@ -132,10 +132,39 @@ def test_errors_match_the_package():
         PlyData.read(io.BytesIO(b"plx\nformat ascii 1.0\nend_header\n"))
     with pytest.raises(PlyHeaderParseError, match="unknown data type"):
         PlyData.read(io.BytesIO(b"ply\nformat ascii 1.0\nelement vertex 1\nproperty half x\nend_header\n0\n"))
-    with pytest.raises(PlyHeaderParseError, match="list properties"):
-        PlyData.read(io.BytesIO(b"ply\nformat ascii 1.0\nelement face 0\nproperty list uchar int vertex_indices\nend_header\n"))
+    with pytest.raises(PlyHeaderParseError, match="integer type"):
+        PlyData.read(io.BytesIO(b"ply\nformat ascii 1.0\nelement face 0\nproperty list float int vertex_indices\nend_header\n"))
     trunc = b"ply\nformat binary_little_endian 1.0\nelement vertex 2\nproperty float x\nend_header\n\0\0\0\0\0\0"
     with pytest.raises(PlyElementParseError, match="early end-of-file"):
         PlyData.read(io.BytesIO(trunc))
     with pytest.raises(PlyElementParseError, match="early end-of-line"):
         PlyData.read(io.BytesIO(b"ply\nformat ascii 1.0\nelement vertex 1\nproperty float x\nproperty float y\nend_header\n1\n"))
+
+
+def test_mesh_with_face_lists_loads_its_vertices():
+    """Not on the path (both call sites use scalar vertex elements), but a mesh PLY given to fetchPly must still load."""
+    text = (b"ply\nformat ascii 1.0\nelement vertex 4\nproperty float x\nproperty float y\nproperty float z\n"
+            b"element face 2\nproperty list uchar int vertex_indices\nproperty uchar flag\nend_header\n"
+            b"0 0 0\n1 0 0\n0 1 0\n0 0 1\n3 0 1 2 7\n4 0 1 2 3 9\n")
+    ply = PlyData.read(io.BytesIO(text))
+    assert ply['vertex']['x'].tolist() == [0.0, 1.0, 0.0, 0.0]
+    faces = ply['face']
+    assert str(faces.properties[0]) == "property list uchar int vertex_indices"
+    assert [f.tolist() for f in faces['vertex_indices']] == [[0, 1, 2], [0, 1, 2, 3]] and faces['flag'].tolist() == [7, 9]
+    assert faces['vertex_indices'][0].dtype == np.int32
+    for kw in (dict(byte_order='<'), dict(byte_order='>'), dict(text=True)):
+        buf = io.BytesIO()
+        PlyData(ply.elements, **kw).write(buf)
+        again = PlyData.read(io.BytesIO(buf.getvalue()))
+        assert [f.tolist() for f in again['face']['vertex_indices']] == [[0, 1, 2], [0, 1, 2, 3]], kw
+        assert again['face']['flag'].tolist() == [7, 9] and again['vertex']['z'].tolist() == [0.0, 0.0, 0.0, 1.0]
+    buf = io.BytesIO()
+    PlyData(ply.elements, byte_order='<').write(buf)
+    body = buf.getvalue().split(b"end_header\n", 1)[1]
+    assert len(body) == 4 * 12 + (1 + 3 * 4 + 1) + (1 + 4 * 4 + 1)
+    # describe(): object column -> list property with the package's default types (uchar count, int values)
+    tri = np.empty(1, dtype=[('vertex_indices', 'O')])
+    tri['vertex_indices'][0] = np.array([2, 1, 0])
+    assert str(PlyElement.describe(tri, 'face').properties[0]) == "property list uchar int vertex_indices"
+    with pytest.raises(PlyElementParseError, match="early end-of-line"):
+        PlyData.read(io.BytesIO(text.replace(b"3 0 1 2 7", b"3 0 1")))
