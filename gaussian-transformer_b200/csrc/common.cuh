@@ -47,9 +47,9 @@ __host__ __device__ inline size_t align_up(size_t v) { return (v + ALIGN - 1) & 
 // binning
 //   point_list u32[R] (depth-sorted gaussian ids, tile after tile)
 // bwd
-//   acc0 float4[P]: dL_dcolor.rgb, dL_dopacity;  acc1 float4[P]: dL_dmean2D.xy, dL_dconic.xx, .xy;
-//   acc2 float[P]: dL_dconic.yy   (SoA so that preprocess_bwd reads them with coalesced 128-bit loads).
-//   acc1 / acc2 hold the sums WITHOUT their per-Gaussian constant factors; finish_2d_grads() applies them.
+//   acc0 float4[P]: dL_dcolor.rgb, dL_dopacity;  acc1 float4[P]: sum q dx, sum q dy, sum q dx dx, sum q dx dy;
+//   acc2 float[P]: sum q dy dy   (SoA so that preprocess_bwd reads them with coalesced 128-bit loads).
+//   acc1 / acc2 are raw moments of q = G * dL/dalpha; finish_2d_grads() turns them into dL_dmean2D / dL_dconic.
 struct GeomView {
   float4* g0;
   float4* g1;
@@ -224,21 +224,18 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
-// render_bwd accumulates  sum q*(dx A + dy B), sum q*(dx B + dy C), sum q dx dx, sum q dx dy, sum q dy dy  with
-// q = G * dL/dalpha; the reference's 2-D gradients (backward.cu:541-551) are these times per-Gaussian constants.
-__device__ __forceinline__ void finish_2d_grads(float opacity, int W, int H, float4& B, float& Cyy) {
-  const float mo = -opacity;
-  B.x *= mo * (0.5f * W);
-  B.y *= mo * (0.5f * H);
+// render_bwd accumulates the raw moments  sum q dx, sum q dy, sum q dx dx, sum q dx dy, sum q dy dy  with
+// q = G * dL/dalpha and (dx, dy) = mean2D - pixel; the reference's 2-D gradients (backward.cu:541-551) are linear in
+// them with per-Gaussian coefficients (conic, opacity, -1, -0.5, 0.5*W, 0.5*H), applied here once per Gaussian.
+// con_o = (conic A, B, C, opacity) as the forward saw them.
+__device__ __forceinline__ void finish_2d_grads(float4 con_o, int W, int H, float4& B, float& Cyy) {
+  const float mo = -con_o.w;
+  const float sx = B.x, sy = B.y;
+  B.x = mo * (0.5f * W) * (con_o.x * sx + con_o.y * sy);
+  B.y = mo * (0.5f * H) * (con_o.y * sx + con_o.z * sy);
   B.z *= 0.5f * mo;
   B.w *= 0.5f * mo;
   Cyy *= 0.5f * mo;
-}
-
-// Vector float atomics (sm_90+): one RED for four consecutive floats.
-__device__ __forceinline__ void red_add_v4(float4* addr, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
-               : "memory");
 }
 
 }  // namespace gsr

@@ -101,6 +101,28 @@ struct ScopedStage {
 
 bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
+// Development / test switches, read from the environment ONCE per process (not per call).
+int env_switch(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return (v && v[0] >= '0' && v[0] <= '9') ? atoi(v) : dflt;
+}
+std::atomic<int> g_force_bin_cta{env_switch("GSR_BIN_CTA", -1)};  // -1 = by list size, 0 / 1 = forced
+std::atomic<int> g_render_bwd{env_switch("GSR_RENDER_BWD", 2)};   // 1 = one pixel per thread, 2 = two (default)
+std::atomic<long long> g_launches{0};                             // kernels launched by this library (gsr_launch_count)
+#define GSR_LAUNCHED(n) g_launches.fetch_add((n), std::memory_order_relaxed)
+
+// Per-device one-time kernel attributes (opt-in shared memory above 48 KB); the per-call path only reads a flag.
+int device_setup() {
+  static std::atomic<int> done[64];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return cuda_fail(cudaGetLastError(), "cudaGetDevice");
+  if (dev >= 0 && dev < 64 && done[dev].load(std::memory_order_acquire)) return GSR_OK;
+  GSR_CUDA(cudaFuncSetAttribute(bin_count_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)BINC_SMEM_MAX), "bin_count smem attribute");
+  if (dev >= 0 && dev < 64) done[dev].store(1, std::memory_order_release);
+  return GSR_OK;
+}
+
 int check_inputs(const gsr_inputs* in) {
   if (!in) return fail(GSR_ERR_INVALID, "gsr_inputs is NULL");
   if (in->P < 0 || in->W <= 0 || in->H <= 0) return fail(GSR_ERR_INVALID, "bad P/W/H");
@@ -155,6 +177,18 @@ extern "C" {
 int gsr_version(void) { return 100; }
 int gsr_compiled_arch(void) { return 100; }
 const char* gsr_last_error(void) { return g_err.c_str(); }
+
+int gsr_set_option(const char* name, int32_t value) {
+  if (!name) return fail(GSR_ERR_INVALID, "gsr_set_option: NULL name");
+  if (!strcmp(name, "bin_cta")) g_force_bin_cta.store(value < 0 ? -1 : (value != 0));
+  else if (!strcmp(name, "render_bwd")) g_render_bwd.store(value == 1 ? 1 : 2);
+  else return fail(GSR_ERR_INVALID, std::string("gsr_set_option: unknown option ") + name);
+  return GSR_OK;
+}
+
+int64_t gsr_launch_count(int reset) {
+  return reset ? g_launches.exchange(0) : g_launches.load();
+}
 
 int gsr_profile_enable(int on) {
   g_prof.on.store(on != 0);
@@ -223,7 +257,7 @@ int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, c
   if (P < 0) return fail(GSR_ERR_INVALID, "gsr_mark_visible: P < 0");
   if (P == 0) return GSR_OK;
   if (!means3D || !viewmatrix || !present) return fail(GSR_ERR_INVALID, "gsr_mark_visible: NULL pointer");
-  mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, viewmatrix, present);
+  mark_visible_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, means3D, viewmatrix, present), GSR_LAUNCHED(1);
   GSR_STAGE("mark_visible", 0, stream);
   return GSR_OK;
 }
@@ -257,12 +291,12 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
     preprocess_fwd_kernel<true><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
                                                             in->rotations, in->opacities, in->sh, nullptr,
                                                             in->colors_precomp, in->cov3D_precomp, cam,
-                                                            in->prefiltered, radii, g, im.ctrl);
+                                                            in->prefiltered, radii, g, im.ctrl), GSR_LAUNCHED(1);
   else
     preprocess_fwd_kernel<false><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
                                                              in->rotations, in->opacities, in->sh, sh_rest,
                                                              in->colors_precomp, in->cov3D_precomp, cam,
-                                                             in->prefiltered, radii, g, im.ctrl);
+                                                             in->prefiltered, radii, g, im.ctrl), GSR_LAUNCHED(1);
   GSR_STAGE("preprocess_fwd", in->debug, stream);
   }
   // depth sort of the P Gaussians: 4 stable 8-bit passes, result in keys[0] / vals[0]
@@ -271,12 +305,12 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   ScopedStage prof_(GSR_STAGE_DEPTH_SORT, stream);
   for (int pass = 0; pass < 4; pass++) {
     const int src = pass & 1, dst = src ^ 1, shift = 8 * pass;
-    radix_hist_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], in->P, shift, n_cta, g.cta_hist);
+    radix_hist_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], in->P, shift, n_cta, g.cta_hist), GSR_LAUNCHED(1);
     uint32_t* digit_total = g.cta_hist + (size_t)256 * n_cta;
-    radix_rowscan_kernel<<<256, 256, 0, stream>>>(g.cta_hist, n_cta, digit_total);
+    radix_rowscan_kernel<<<256, 256, 0, stream>>>(g.cta_hist, n_cta, digit_total), GSR_LAUNCHED(1);
     radix_scatter_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], pass == 0 ? nullptr : g.vals[src], in->P,
                                                           shift, n_cta, g.cta_hist, digit_total, g.keys[dst],
-                                                          g.vals[dst]);
+                                                          g.vals[dst]), GSR_LAUNCHED(1);
     GSR_STAGE("depth_sort", in->debug, stream);
   }
   }
@@ -285,23 +319,20 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   if (bin_parallel(cam.gx, cam.gy, plan)) {
     // parallel binning, counting half: one CTA per chunk, all tiles in shared memory
     const size_t smem = binc_smem(cam.gx, cam.gy);
-    GSR_CUDA(cudaFuncSetAttribute(bin_count_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
-             "bin_count smem attribute");
+    if (int rc = device_setup()) return rc;
     bin_count_cta_kernel<<<dim3(plan.n_chunks, binc_bands(cam.gx, cam.gy)), BINC_THREADS, smem, stream>>>(
-        in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan.chunk, g.rects, im.matrix);
+        in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan.chunk, g.rects, im.matrix), GSR_LAUNCHED(1);
   } else {
     // order-preserving serial walk (tile grids too large for a shared-memory table), counting half
     const int tasks = plan.n_chunks * plan.n_bands;
-    const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
-    GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
-             "bin_pass smem attribute");
+    const int bin_smem = BIN_WARPS * plan.band_tiles * 4;  // <= 32 KB (BAND_TILES_MAX): no opt-in needed
     bin_pass_kernel<false><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
-        in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, nullptr, nullptr, nullptr, 0u);
+        in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, nullptr, nullptr, nullptr, 0u), GSR_LAUNCHED(1);
   }
   GSR_STAGE("bin_count", in->debug, stream);
-  column_scan_kernel<<<((int)T + 31) / 32, 1024, 0, stream>>>(im.matrix, plan.n_chunks, (int)T, im.tile_count);
+  column_scan_kernel<<<((int)T + 31) / 32, 1024, 0, stream>>>(im.matrix, plan.n_chunks, (int)T, im.tile_count), GSR_LAUNCHED(1);
   GSR_STAGE("column_scan", in->debug, stream);
-  tile_scan_kernel<<<1, 1024, 0, stream>>>((int)T, im.tile_count, im.ranges, im.ctrl);
+  tile_scan_kernel<<<1, 1024, 0, stream>>>((int)T, im.tile_count, im.ranges, im.ctrl), GSR_LAUNCHED(1);
   GSR_STAGE("tile_scan", in->debug, stream);
   }
   // ctrl[CTRL_R_LO..HI] -> host_result[0] (little endian int64), flags -> [1]
@@ -343,9 +374,9 @@ int forward_post_impl(const gsr_inputs* in, const void* geom, void* binning, voi
       const int tasks = plan.n_chunks * plan.n_bands;
       const int bin_smem = BIN_WARPS * plan.band_tiles * 4;
       // lists that outgrow the L2 (or chunks with long serial walks) take the CTA-cooperative, band-major kernel
-      const char* force = getenv("GSR_BIN_CTA");  // dev / test switch: "0" / "1"
+      const int force_cta = g_force_bin_cta.load(std::memory_order_relaxed);
       const bool long_lists = (size_t)R * 4 > ((size_t)64 << 20) || plan.chunk > 1024;
-      const bool cta = plan.chunk >= 256 && (force ? force[0] == '1' : long_lists);
+      const bool cta = plan.chunk >= 256 && (force_cta >= 0 ? force_cta == 1 : long_lists);
       if (cta) {
         // Every band CTA scans its whole chunk, so taller bands mean less scanning but a larger cursor table per
         // warp: ~960 tiles per band (30 KB per CTA) measured best at both 1080p (8 rows: 552 -> 422 us at 3 M
@@ -354,18 +385,14 @@ int forward_post_impl(const gsr_inputs* in, const void* geom, void* binning, voi
         cp.rows_per_band = std::max(1, std::min({960 / cam.gx, cam.gy, 1023}));
         cp.n_bands = (cam.gy + cp.rows_per_band - 1) / cp.rows_per_band;
         cp.band_tiles = cp.rows_per_band * cam.gx;
-        const int cta_smem = BIN_WARPS * cp.band_tiles * 4;
-        GSR_CUDA(cudaFuncSetAttribute(bin_scatter_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, cta_smem),
-                 "bin_scatter smem attribute");
+        const int cta_smem = BIN_WARPS * cp.band_tiles * 4;  // <= ~20 KB: no opt-in needed
         bin_scatter_cta_kernel<<<cp.n_chunks * cp.n_bands, BIN_WARPS * 32, cta_smem, stream>>>(
             in->P, g.vals[0], g.g0, cam.gx, cam.gy, cp, im.matrix, im.ranges, b.point_list,
-            bin_parallel(cam.gx, cam.gy, plan) ? g.rects : nullptr, guard, cap);
+            bin_parallel(cam.gx, cam.gy, plan) ? g.rects : nullptr, guard, cap), GSR_LAUNCHED(1);
       } else {
-        GSR_CUDA(cudaFuncSetAttribute(bin_pass_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, bin_smem),
-                 "bin_pass smem attribute");
         bin_pass_kernel<true><<<(tasks + BIN_WARPS - 1) / BIN_WARPS, BIN_WARPS * 32, bin_smem, stream>>>(
             in->P, g.vals[0], g.g0, cam.gx, cam.gy, plan, im.matrix, im.ranges, b.point_list,
-            bin_parallel(cam.gx, cam.gy, plan) ? g.rects : nullptr, guard, cap);
+            bin_parallel(cam.gx, cam.gy, plan) ? g.rects : nullptr, guard, cap), GSR_LAUNCHED(1);
       }
       GSR_STAGE("bin_scatter", in->debug, stream);
     }
@@ -374,22 +401,19 @@ int forward_post_impl(const gsr_inputs* in, const void* geom, void* binning, voi
   dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
   render_fwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, g.g0, g.g1, g.g2,
                                                 in->colors_precomp, in->bg, im.final_T, im.n_contrib, out_color,
-                                                guard, cap);
+                                                guard, cap), GSR_LAUNCHED(1);
   GSR_STAGE("render_fwd", in->debug, stream);
   return GSR_OK;
 }
 
-// one event per host thread for gsr_forward's "R is on the host" wait
+// one event per (host thread, device) for gsr_forward's "R is on the host" wait; created once, never re-created
 cudaEvent_t forward_event() {
-  thread_local cudaEvent_t ev = nullptr;
-  thread_local int ev_dev = -1;
+  constexpr int MAX_DEV = 64;
+  thread_local cudaEvent_t ev[MAX_DEV] = {};
   int dev = 0;
-  cudaGetDevice(&dev);
-  if (ev == nullptr || ev_dev != dev) {
-    if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-    ev_dev = dev;
-  }
-  return ev;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= MAX_DEV) return nullptr;
+  if (ev[dev] == nullptr && cudaEventCreateWithFlags(&ev[dev], cudaEventDisableTiming) != cudaSuccess) return nullptr;
+  return ev[dev];
 }
 }  // namespace
 
@@ -412,7 +436,10 @@ int gsr_forward(const gsr_inputs* in, void* geom, void* binning, int64_t capacit
   GSR_CUDA(cudaEventRecord(ev, stream), "record R event");
   if (capacity_R > 0 && binning) {
     // phase 2 goes out BEFORE the host knows num_rendered: no GPU idle time across the round trip
-    if (int rc = forward_post_impl(in, geom, binning, image, capacity_R, true, out_color, stream)) return rc;
+    if (int rc = forward_post_impl(in, geom, binning, image, capacity_R, true, out_color, stream)) {
+      cudaEventSynchronize(ev);  // the async copy into the caller's host_result must not outlive this call
+      return rc;
+    }
   }
   GSR_CUDA(cudaEventSynchronize(ev), "wait for num_rendered");
   return GSR_OK;
@@ -435,9 +462,14 @@ int gsr_backward_blend(const gsr_inputs* in, const void* geom, const void* binni
   GSR_CUDA(cudaMemsetAsync(bwd_scratch, 0, bwd_bytes((size_t)in->P), stream), "memset bwd accumulators");
   if (R > 0) {
     ScopedStage prof_(GSR_STAGE_RENDER_BWD, stream);
-    dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
-    render_bwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0, g.g1, g.g2,
-                                                  in->colors_precomp, im.final_T, im.n_contrib, dL_dpix, bw);
+    dim3 grid(cam.gx, cam.gy);
+    if (g_render_bwd.load(std::memory_order_relaxed) == 1)
+      render_bwd_kernel<<<grid, TILE_PIX, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0, g.g1, g.g2,
+                                                       in->colors_precomp, im.final_T, im.n_contrib, dL_dpix, bw), GSR_LAUNCHED(1);
+    else
+      render_bwd2_kernel<<<grid, RB2_THREADS, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0, g.g1,
+                                                           g.g2, in->colors_precomp, im.final_T, im.n_contrib,
+                                                           dL_dpix, bw), GSR_LAUNCHED(1);
     GSR_STAGE("render_bwd", in->debug, stream);
   }
   return GSR_OK;
@@ -487,25 +519,25 @@ int backward_geometry_impl(const gsr_inputs* in, const int32_t* radii, const voi
   if (split && in->M == 16) {
     preprocess_bwd_staged_kernel<16, true><<<pb_blocks, PB_THREADS, PB_THREADS * 45 * 4, stream>>>(
         in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, in->sh_rest, in->cov3D_precomp, cam,
-        radii, g.g2, bw, out);
+        radii, g.g2, bw, out), GSR_LAUNCHED(1);
   } else if (split) {
     preprocess_bwd_staged_kernel<4, true><<<pb_blocks, PB_THREADS, PB_THREADS * 9 * 4 + 16, stream>>>(
         in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, in->sh_rest, in->cov3D_precomp, cam,
-        radii, g.g2, bw, out);
+        radii, g.g2, bw, out), GSR_LAUNCHED(1);
   } else if (staged && in->M == 16) {
     const int smem = PB_THREADS * 13 * 16;
     preprocess_bwd_staged_kernel<16, false><<<pb_blocks, PB_THREADS, smem, stream>>>(
         in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, nullptr, in->cov3D_precomp, cam, radii,
-        g.g2, bw, out);
+        g.g2, bw, out), GSR_LAUNCHED(1);
   } else if (staged) {
     const int smem = PB_THREADS * 3 * 16;
     preprocess_bwd_staged_kernel<4, false><<<pb_blocks, PB_THREADS, smem, stream>>>(
         in->P, in->D, in->means3D, in->scales, in->rotations, g.g1, in->sh, nullptr, in->cov3D_precomp, cam, radii,
-        g.g2, bw, out);
+        g.g2, bw, out), GSR_LAUNCHED(1);
   } else {
     preprocess_bwd_kernel<<<pb_blocks, PB_THREADS, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
                                                                 in->rotations, g.g1, in->sh, in->cov3D_precomp,
-                                                                cam, radii, g.g2, bw, out);
+                                                                cam, radii, g.g2, bw, out), GSR_LAUNCHED(1);
   }
   GSR_STAGE("preprocess_bwd", in->debug, stream);
   return GSR_OK;
@@ -552,7 +584,7 @@ int gsr_backward_sh_factors(int32_t P, const void* geom, const void* bwd_scratch
   if (!geom || !bwd_scratch || !factors) return fail(GSR_ERR_INVALID, "gsr_backward_sh_factors: NULL pointer");
   GeomView g = geom_view(const_cast<void*>(geom), (size_t)P);
   BwdView bw = bwd_view(const_cast<void*>(bwd_scratch), (size_t)P);
-  sh_acc_factors_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.g2, bw.acc0, factors);
+  sh_acc_factors_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.g2, bw.acc0, factors), GSR_LAUNCHED(1);
   GSR_STAGE("sh_acc_factors", 0, stream);
   return GSR_OK;
 }
@@ -563,7 +595,7 @@ int gsr_sh_color_factors(int32_t P, const void* geom, const float* dL_dcolors, f
   if (P == 0) return GSR_OK;
   if (!geom || !dL_dcolors || !factors) return fail(GSR_ERR_INVALID, "gsr_sh_color_factors: NULL pointer");
   GeomView g = geom_view(const_cast<void*>(geom), (size_t)P);
-  sh_color_factors_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.g2, dL_dcolors, factors);
+  sh_color_factors_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, g.g2, dL_dcolors, factors), GSR_LAUNCHED(1);
   GSR_STAGE("sh_color_factors", 0, stream);
   return GSR_OK;
 }
@@ -579,10 +611,10 @@ int gsr_sh_grad_from_factors(int32_t P, int32_t D, int32_t M, int32_t V, const f
   const int blocks = (P + PB_THREADS - 1) / PB_THREADS;
   if (M == 16 && aligned16(dL_dsh))
     sh_grad_from_factors_kernel<true><<<blocks, PB_THREADS, PB_THREADS * 13 * 16, stream>>>(
-        P, D, M, V, means3D, campos, factors, dL_dsh, accumulate);
+        P, D, M, V, means3D, campos, factors, dL_dsh, accumulate), GSR_LAUNCHED(1);
   else
     sh_grad_from_factors_kernel<false><<<blocks, PB_THREADS, 0, stream>>>(P, D, M, V, means3D, campos, factors,
-                                                                         dL_dsh, accumulate);
+                                                                         dL_dsh, accumulate), GSR_LAUNCHED(1);
   GSR_STAGE("sh_grad_from_factors", 0, stream);
   return GSR_OK;
 }
@@ -630,24 +662,24 @@ int gsr_knn_dist2(int32_t P, const float* points, float* mean_dist2, void* scrat
   const int blocks = (P + 255) / 256;
   GSR_CUDA(cudaMemsetAsync(v.bounds, 0xff, 12, stream), "knn memset min");
   GSR_CUDA(cudaMemsetAsync(v.bounds + 3, 0x00, 12, stream), "knn memset max");
-  knn_bounds_kernel<<<blocks < 592 ? blocks : 592, 256, 0, stream>>>(P, points, v.bounds);
-  knn_morton_kernel<<<blocks, 256, 0, stream>>>(P, points, v.bounds, v.keys[0]);
+  knn_bounds_kernel<<<blocks < 592 ? blocks : 592, 256, 0, stream>>>(P, points, v.bounds), GSR_LAUNCHED(1);
+  knn_morton_kernel<<<blocks, 256, 0, stream>>>(P, points, v.bounds, v.keys[0]), GSR_LAUNCHED(1);
   GSR_STAGE("knn_morton", 0, stream);
   const int n_cta = (int)sort_ctas((size_t)P);
   for (int pass = 0; pass < 4; pass++) {  // 30-bit codes: 4 stable 8-bit passes, result in keys[0] / vals[0]
     const int src = pass & 1, dst = src ^ 1, shift = 8 * pass;
-    radix_hist_kernel<<<n_cta, RS_THREADS, 0, stream>>>(v.keys[src], P, shift, n_cta, v.cta_hist);
+    radix_hist_kernel<<<n_cta, RS_THREADS, 0, stream>>>(v.keys[src], P, shift, n_cta, v.cta_hist), GSR_LAUNCHED(1);
     uint32_t* digit_total = v.cta_hist + (size_t)256 * n_cta;
-    radix_rowscan_kernel<<<256, 256, 0, stream>>>(v.cta_hist, n_cta, digit_total);
+    radix_rowscan_kernel<<<256, 256, 0, stream>>>(v.cta_hist, n_cta, digit_total), GSR_LAUNCHED(1);
     radix_scatter_kernel<<<n_cta, RS_THREADS, 0, stream>>>(v.keys[src], pass == 0 ? nullptr : v.vals[src], P, shift,
-                                                          n_cta, v.cta_hist, digit_total, v.keys[dst], v.vals[dst]);
+                                                          n_cta, v.cta_hist, digit_total, v.keys[dst], v.vals[dst]), GSR_LAUNCHED(1);
   }
   GSR_STAGE("knn_sort", 0, stream);
   const int nb = (P + KNN_BOX - 1) / KNN_BOX, ns = (nb + KNN_SUPER - 1) / KNN_SUPER;
-  knn_gather_kernel<<<blocks, 256, 0, stream>>>(P, points, v.vals[0], v.sorted);
-  knn_boxes_kernel<<<nb, KNN_BOX, 0, stream>>>(P, v.sorted, v.boxes);
-  knn_supers_kernel<<<ns, 32, 0, stream>>>(nb, v.boxes, v.supers);
-  knn_search_kernel<<<nb, KNN_BOX, 0, stream>>>(P, v.sorted, nb, v.boxes, ns, v.supers, mean_dist2);
+  knn_gather_kernel<<<blocks, 256, 0, stream>>>(P, points, v.vals[0], v.sorted), GSR_LAUNCHED(1);
+  knn_boxes_kernel<<<nb, KNN_BOX, 0, stream>>>(P, v.sorted, v.boxes), GSR_LAUNCHED(1);
+  knn_supers_kernel<<<ns, 32, 0, stream>>>(nb, v.boxes, v.supers), GSR_LAUNCHED(1);
+  knn_search_kernel<<<nb, KNN_BOX, 0, stream>>>(P, v.sorted, nb, v.boxes, ns, v.supers, mean_dist2), GSR_LAUNCHED(1);
   GSR_STAGE("knn_search", 0, stream);
   return GSR_OK;
 }
@@ -669,13 +701,13 @@ int gsr_l1_ssim_loss(int32_t C, int32_t H, int32_t W, const float* img, const fl
   float* maps = (float*)((char*)scratch + align_up(LOSS_SLOTS * sizeof(LossAcc)));
   GSR_CUDA(cudaMemsetAsync(acc, 0, LOSS_SLOTS * sizeof(LossAcc), stream), "loss memset");
   const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
-  loss_pass1_kernel<<<grid, LOSS_THREADS, 0, stream>>>(H, W, img, gt, maps, acc);
+  loss_pass1_kernel<<<grid, LOSS_THREADS, 0, stream>>>(H, W, img, gt, maps, acc), GSR_LAUNCHED(1);
   GSR_STAGE("loss_pass1", 0, stream);
   const double n = (double)C * H * W;
-  loss_finish_kernel<<<1, 1, 0, stream>>>(acc, n, lambda_dssim, out3);
+  loss_finish_kernel<<<1, 1, 0, stream>>>(acc, n, lambda_dssim, out3), GSR_LAUNCHED(1);
   if (dL_dimg) {
     loss_pass2_kernel<<<grid, LOSS_THREADS, 0, stream>>>(H, W, img, gt, maps, (float)((1.0 - lambda_dssim) / n),
-                                                    (float)(lambda_dssim / n), nullptr, dL_dimg);
+                                                    (float)(lambda_dssim / n), nullptr, dL_dimg), GSR_LAUNCHED(1);
     GSR_STAGE("loss_pass2", 0, stream);
   }
   return GSR_OK;
@@ -690,7 +722,7 @@ int gsr_l1_ssim_backward(int32_t C, int32_t H, int32_t W, const float* img, cons
   const dim3 grid((W + LT - 1) / LT, (H + LT - 1) / LT, C);
   const double n = (double)C * H * W;
   loss_pass2_kernel<<<grid, LOSS_THREADS, 0, stream>>>(H, W, img, gt, maps, (float)((1.0 - lambda_dssim) / n),
-                                                  (float)(lambda_dssim / n), upstream, dL_dimg);
+                                                  (float)(lambda_dssim / n), upstream, dL_dimg), GSR_LAUNCHED(1);
   GSR_STAGE("loss_pass2", 0, stream);
   return GSR_OK;
 }
@@ -707,7 +739,7 @@ int gsr_activate(int32_t P, const float* opacity_raw, const float* scaling_raw, 
     return fail(GSR_ERR_INVALID, "gsr_activate: rotation arrays must be 16-byte aligned");
   activate_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, opacity_raw, scaling_raw,
                                                        reinterpret_cast<const float4*>(rotation_raw), opacities, scales,
-                                                       reinterpret_cast<float4*>(rotations));
+                                                       reinterpret_cast<float4*>(rotations)), GSR_LAUNCHED(1);
   GSR_STAGE("activate", 0, stream);
   return GSR_OK;
 }
@@ -726,7 +758,7 @@ int gsr_activate_backward(int32_t P, const float* opacity_raw, const float* scal
   activate_bwd_kernel<<<(P + 255) / 256, 256, 0, stream>>>(
       P, opacity_raw, scaling_raw, reinterpret_cast<const float4*>(rotation_raw), dL_dopacities, dL_dscales,
       reinterpret_cast<const float4*>(dL_drotations), dL_dopacity_raw, dL_dscaling_raw,
-      reinterpret_cast<float4*>(dL_drotation_raw));
+      reinterpret_cast<float4*>(dL_drotation_raw)), GSR_LAUNCHED(1);
   GSR_STAGE("activate_bwd", 0, stream);
   return GSR_OK;
 }
@@ -739,7 +771,7 @@ int gsr_densification_stats(int32_t P, const int32_t* radii, const float* dL_dme
   if (!radii || !dL_dmeans2D || !max_radii2D || !xyz_gradient_accum || !denom)
     return fail(GSR_ERR_INVALID, "gsr_densification_stats: NULL pointer");
   densify_stats_kernel<<<(P + 255) / 256, 256, 0, stream>>>(P, radii, dL_dmeans2D, max_radii2D, xyz_gradient_accum,
-                                                            denom);
+                                                            denom), GSR_LAUNCHED(1);
   GSR_STAGE("densify_stats", 0, stream);
   return GSR_OK;
 }
@@ -777,7 +809,7 @@ int gsr_adam_step(int32_t n_groups, const gsr_adam_group* groups, double beta1, 
   a.beta2 = (float)beta2;
   a.w2 = (float)(1.0 - beta2);
   a.eps = (float)eps;
-  adam_step_kernel<<<(unsigned)blocks, ADAM_THREADS, 0, stream>>>(a);
+  adam_step_kernel<<<(unsigned)blocks, ADAM_THREADS, 0, stream>>>(a), GSR_LAUNCHED(1);
   GSR_STAGE("adam_step", 0, stream);
   return GSR_OK;
 }

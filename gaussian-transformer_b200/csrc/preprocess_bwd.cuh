@@ -284,7 +284,7 @@ __global__ void __launch_bounds__(PB_THREADS, 5) preprocess_bwd_staged_kernel(
     A = __ldcs(acc.acc0 + i);
     B = __ldcs(acc.acc1 + i);
     Cyy = __ldcs(acc.acc2 + i);
-    finish_2d_grads(__ldg(&g1[i].w), cam.W, cam.H, B, Cyy);  // opacity as the forward saw it
+    finish_2d_grads(__ldg(g1 + i), cam.W, cam.H, B, Cyy);  // opacity as the forward saw it
   }
   __syncthreads();
   if (D > 0) {  // coefficient rows of the visible Gaussians, coalesced (degree 0 needs no coefficient)
@@ -420,7 +420,7 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_bwd_kernel(
   const float4 A = acc.acc0[i];
   float4 B = acc.acc1[i];
   float Cyy = acc.acc2[i];
-  finish_2d_grads(__ldg(&g1[i].w), cam.W, cam.H, B, Cyy);  // opacity as the forward saw it
+  finish_2d_grads(__ldg(g1 + i), cam.W, cam.H, B, Cyy);  // opacity as the forward saw it
   out.dL_dcolors[3 * I] = A.x; out.dL_dcolors[3 * I + 1] = A.y; out.dL_dcolors[3 * I + 2] = A.z;
   out.dL_dopacity[I] = A.w;
   out.dL_dmeans2D[3 * I] = B.x; out.dL_dmeans2D[3 * I + 1] = B.y; out.dL_dmeans2D[3 * I + 2] = 0.f;

@@ -38,7 +38,7 @@ EXPORTS = (
     "gsr_loss_scratch_bytes", "gsr_l1_ssim_loss", "gsr_l1_ssim_backward",
     "gsr_backward_blend", "gsr_backward_geometry", "gsr_backward_sh_factors",
     "gsr_adam_step", "gsr_forward", "gsr_backward_geometry_split",
-    "gsr_activate", "gsr_activate_backward", "gsr_densification_stats",
+    "gsr_activate", "gsr_activate_backward", "gsr_densification_stats", "gsr_launch_count", "gsr_set_option",
 )
 STAGES = ("preprocess_fwd", "depth_sort", "bin_count", "bin_scatter", "render_fwd", "render_bwd", "preprocess_bwd")
 
@@ -77,6 +77,9 @@ def load(path=LIB_PATH):
     lib.gsr_sh_color_factors.argtypes = [i32, vp, vp, vp, vp]
     lib.gsr_sh_grad_from_factors.argtypes = [i32, i32, i32, i32, vp, vp, vp, vp, i32, vp]
     lib.gsr_get_views.argtypes = [i32, i64, i32, i32, vp, vp, vp, ctypes.POINTER(gsr_views)]
+    lib.gsr_launch_count.argtypes = [ctypes.c_int]
+    lib.gsr_launch_count.restype = ctypes.c_int64
+    lib.gsr_set_option.argtypes = [ctypes.c_char_p, i32]
     lib.gsr_profile_enable.argtypes = [ctypes.c_int]
     lib.gsr_profile_read.argtypes = [ctypes.POINTER(ctypes.c_float), ctypes.POINTER(ctypes.c_int32)]
     for name in ("gsr_profile_enable", "gsr_profile_read", "gsr_scratch_bytes", "gsr_forward_pre", "gsr_forward_post", "gsr_backward", "gsr_mark_visible",
@@ -98,6 +101,16 @@ def scratch_bytes(P, R, W, H):
     g, b, i, w = (ctypes.c_size_t() for _ in range(4))
     check(lib.gsr_scratch_bytes(P, R, W, H, ctypes.byref(g), ctypes.byref(b), ctypes.byref(i), ctypes.byref(w)))
     return g.value, b.value, i.value, w.value
+
+
+def set_option(name, value):
+    """Development / test switch of the library (include/gsrast.h gsr_set_option)."""
+    check(lib.gsr_set_option(name.encode(), int(value)))
+
+
+def launch_count(reset=False):
+    """Kernels launched by the library in this process since the last reset."""
+    return int(lib.gsr_launch_count(int(reset)))
 
 
 def profile_enable(on=True):

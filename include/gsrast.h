@@ -270,15 +270,22 @@ GSR_API int gsr_mark_visible(int32_t P, const float* means3D, const float* viewm
  * since the previous read, and recycles the events. */
 enum {
   GSR_STAGE_PREPROCESS_FWD = 0, /* preprocess_fwd_kernel */
-  GSR_STAGE_DEPTH_SORT = 1,     /* 4 x (radix_hist, exclusive_scan, radix_scatter) */
-  GSR_STAGE_BIN_COUNT = 2,      /* bin_pass<count>, column_scan, tile_scan */
-  GSR_STAGE_BIN_SCATTER = 3,    /* bin_pass<scatter> */
+  GSR_STAGE_DEPTH_SORT = 1,     /* depth sort of the P Gaussians (depth_sort.cuh) */
+  GSR_STAGE_BIN_COUNT = 2,      /* bin_count_cta_kernel (or bin_pass_kernel<false>), column_scan_kernel, tile_scan_kernel */
+  GSR_STAGE_BIN_SCATTER = 3,    /* bin_pass_kernel<true> or bin_scatter_cta_kernel */
   GSR_STAGE_RENDER_FWD = 4,     /* render_fwd_kernel */
-  GSR_STAGE_RENDER_BWD = 5,     /* render_bwd_kernel */
-  GSR_STAGE_PREPROCESS_BWD = 6, /* preprocess_bwd_kernel */
+  GSR_STAGE_RENDER_BWD = 5,     /* render_bwd2_kernel (render_bwd_kernel with option render_bwd = 1) */
+  GSR_STAGE_PREPROCESS_BWD = 6, /* preprocess_bwd_staged_kernel / preprocess_bwd_kernel */
   GSR_STAGE_COUNT = 7
 };
 GSR_API int gsr_profile_enable(int on);
+/* Number of kernels this library has launched in the process since the last reset (every launch site counts
+ * itself); bench.py reports it as gpu_launches.  No reference counterpart. */
+GSR_API int64_t gsr_launch_count(int reset);
+/* Development / test switches (process-wide).  "bin_cta": -1 = pick the scatter kernel by list size (default),
+ * 0 / 1 = force bin_pass_kernel<true> / bin_scatter_cta_kernel; "render_bwd": 2 = two pixels per thread (default),
+ * 1 = one.  Initial values come from the environment variables GSR_BIN_CTA / GSR_RENDER_BWD, read once at load. */
+GSR_API int gsr_set_option(const char* name, int32_t value);
 GSR_API int gsr_profile_read(float* ms /* [GSR_STAGE_COUNT] */, int32_t* counts /* [GSR_STAGE_COUNT] */);
 
 /* Decoded views into the scratch buffers of a finished forward (device

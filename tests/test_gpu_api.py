@@ -160,16 +160,18 @@ def test_dp_step_factored_two_views_one_rank():
         assert rel_err(np_(out[k]).reshape(want.shape), np_(want)) <= 1e-3, k
 
 
-def test_cta_scatter_kernel_writes_the_same_lists(monkeypatch):
+def test_cta_scatter_kernel_writes_the_same_lists():
     """bin_scatter_cta_kernel (taken automatically once point_list outgrows the L2) against bin_pass<true>: identical
     per-tile lists, image and n_contrib."""
-    from diff_gaussian_rasterization import _C
+    from diff_gaussian_rasterization import _C, _lib
     sc = S.scene_S(80000, 640, 360, seed=9, M=16, sh_degree=3)
     d = to_device(sc)
     e = torch.Tensor([])
     res = []
-    for force in ("0", "1"):
-        monkeypatch.setenv("GSR_BIN_CTA", force)
+    for force in (0, 1, -1):
+        _lib.set_option("bin_cta", force)
+        if force < 0:
+            break
         res.append(_C.rasterize_gaussians(d["bg"], d["means3D"], e, d["opacities"], d["scales"], d["rotations"], 1.0, e,
                                           d["viewmatrix"], d["projmatrix"], d["tanfovx"], d["tanfovy"], sc["H"],
                                           sc["W"], d["sh"], 3, d["campos"], False, False))
