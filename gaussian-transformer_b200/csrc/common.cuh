@@ -39,7 +39,8 @@ __host__ __device__ inline size_t align_up(size_t v) { return (v + ALIGN - 1) & 
 //   g1 float4[P]  conic.x, conic.y, conic.z, opacity
 //   g2 float4[P]  r, g, b, flags (bits 0..2 = clamped r/g/b, bits 3.. = tiles_touched)
 //   keys[2] u32[P], vals[2] u32[P]  depth-sort ping-pong (keys = depth bits, 0xffffffff for culled)
-//   cta_hist u32[256 * n_sort_cta + 256]  radix digit histograms (digit-major) + digit totals
+//   cta_hist u32[sort_scratch_words(P)]  sort scratch: onesweep.cuh digit histograms + look-back status words
+//                 (or depth_sort.cuh's digit-major per-CTA histograms + digit totals)
 //   rects uint2[P]  clipped tile rectangle of the k-th Gaussian in depth order (binning.cuh)
 // image
 //   final_T f32[N], n_contrib u32[N], ranges uint2[T], tile_count u32[T], ctrl u32[64],
@@ -74,6 +75,7 @@ struct BwdView {
   float4* acc0;
   float4* acc1;
   float* acc2;
+  unsigned long long* counters;  // 3 test counters in the buffer's tail (render_bwd2_kernel<true> only)
 };
 
 // ctrl[] slots
@@ -84,6 +86,21 @@ enum { CTRL_R_LO = 4, CTRL_R_HI = 5, CTRL_FLAGS = 6, CTRL_WORDS = 64 };  // word
 #endif
 constexpr int SORT_TILE_KEYS = 256 * GSR_SORT_ROUNDS;  // keys per CTA in depth_sort.cuh (RS_TILE)
 inline size_t sort_ctas(size_t P) { return (P + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS; }
+// onesweep.cuh: 4096 keys per tile; scratch words = [4][256] digit histograms, 64 words of tile counters,
+// [4][tiles + groups][256] look-back status words
+#ifndef GSR_OS_KPT
+#define GSR_OS_KPT 16
+#endif
+constexpr int OS_TILE_KEYS = 256 * GSR_OS_KPT;
+inline size_t os_tiles(size_t n) { return (n + OS_TILE_KEYS - 1) / OS_TILE_KEYS; }
+constexpr int OS_GROUP_TILES = 16;
+inline size_t os_groups(size_t n) { return (os_tiles(n) + OS_GROUP_TILES - 1) / OS_GROUP_TILES; }
+inline size_t os_scratch_words(size_t n) { return 4 * 256 + 64 + 4 * (os_tiles(n) + os_groups(n)) * 256; }
+// words of sort scratch behind keys / vals: whichever of the two sorts needs more
+inline size_t sort_scratch_words(size_t P) {
+  const size_t a = 256 * (sort_ctas(P) + 1), b = os_scratch_words(P);
+  return a > b ? a : b;
+}
 // Gaussians per binning chunk (binning.cuh): a power of two >= 1024 with at most 1024 chunks; scenes of up to 64 K
 // Gaussians get chunks of 128 (more parallel walks: 33.7 K Gaussians at 800x450 forward 0.201 -> 0.171 ms; at 200 K
 // Gaussians finer chunks measured 5 % slower, hence the threshold) while the chunks x tiles matrix stays < 32 MB.
@@ -100,7 +117,7 @@ inline size_t bin_chunks(size_t P, size_t T) {
 }
 
 inline size_t geom_bytes(size_t P) {
-  return 3 * align_up(16 * P) + 4 * align_up(4 * P) + align_up(4 * 256 * (sort_ctas(P) + 1)) + align_up(8 * P) + ALIGN;
+  return 3 * align_up(16 * P) + 4 * align_up(4 * P) + align_up(4 * sort_scratch_words(P)) + align_up(8 * P) + ALIGN;
 }
 inline GeomView geom_view(void* base, size_t P) {
   char* p = (char*)base;
@@ -112,7 +129,7 @@ inline GeomView geom_view(void* base, size_t P) {
   v.keys[1] = (uint32_t*)p; p += align_up(4 * P);
   v.vals[0] = (uint32_t*)p; p += align_up(4 * P);
   v.vals[1] = (uint32_t*)p; p += align_up(4 * P);
-  v.cta_hist = (uint32_t*)p; p += align_up(4 * 256 * (sort_ctas(P) + 1));
+  v.cta_hist = (uint32_t*)p; p += align_up(4 * sort_scratch_words(P));
   v.rects = (uint2*)p;
   return v;
 }
@@ -144,7 +161,8 @@ inline BwdView bwd_view(void* base, size_t P) {
   BwdView v;
   v.acc0 = (float4*)p; p += align_up(16 * P);
   v.acc1 = (float4*)p; p += align_up(16 * P);
-  v.acc2 = (float*)p;
+  v.acc2 = (float*)p; p += align_up(4 * P);
+  v.counters = (unsigned long long*)p;  // inside the trailing ALIGN bytes of bwd_bytes()
   return v;
 }
 

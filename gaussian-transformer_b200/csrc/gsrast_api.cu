@@ -14,6 +14,7 @@
 #include "binning.cuh"
 #include "common.cuh"
 #include "depth_sort.cuh"
+#include "onesweep.cuh"
 #include <algorithm>
 #include <cstdlib>
 
@@ -108,6 +109,7 @@ int env_switch(const char* name, int dflt) {
 }
 std::atomic<int> g_force_bin_cta{env_switch("GSR_BIN_CTA", -1)};  // -1 = by list size, 0 / 1 = forced
 std::atomic<int> g_render_bwd{env_switch("GSR_RENDER_BWD", 2)};   // 1 = one pixel per thread, 2 = two (default)
+std::atomic<int> g_sort{env_switch("GSR_SORT", 1)};               // 1 = onesweep.cuh (default), 0 = depth_sort.cuh
 std::atomic<long long> g_launches{0};                             // kernels launched by this library (gsr_launch_count)
 #define GSR_LAUNCHED(n) g_launches.fetch_add((n), std::memory_order_relaxed)
 
@@ -181,7 +183,8 @@ const char* gsr_last_error(void) { return g_err.c_str(); }
 int gsr_set_option(const char* name, int32_t value) {
   if (!name) return fail(GSR_ERR_INVALID, "gsr_set_option: NULL name");
   if (!strcmp(name, "bin_cta")) g_force_bin_cta.store(value < 0 ? -1 : (value != 0));
-  else if (!strcmp(name, "render_bwd")) g_render_bwd.store(value == 1 ? 1 : 2);
+  else if (!strcmp(name, "sort")) g_sort.store(value != 0);
+  else if (!strcmp(name, "render_bwd")) g_render_bwd.store(value == 1 || value == 3 ? value : 2);
   else return fail(GSR_ERR_INVALID, std::string("gsr_set_option: unknown option ") + name);
   return GSR_OK;
 }
@@ -300,18 +303,24 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   GSR_STAGE("preprocess_fwd", in->debug, stream);
   }
   // depth sort of the P Gaussians: 4 stable 8-bit passes, result in keys[0] / vals[0]
-  const int n_cta = (int)sort_ctas((size_t)in->P);
   {
   ScopedStage prof_(GSR_STAGE_DEPTH_SORT, stream);
-  for (int pass = 0; pass < 4; pass++) {
-    const int src = pass & 1, dst = src ^ 1, shift = 8 * pass;
-    radix_hist_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], in->P, shift, n_cta, g.cta_hist), GSR_LAUNCHED(1);
-    uint32_t* digit_total = g.cta_hist + (size_t)256 * n_cta;
-    radix_rowscan_kernel<<<256, 256, 0, stream>>>(g.cta_hist, n_cta, digit_total), GSR_LAUNCHED(1);
-    radix_scatter_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], pass == 0 ? nullptr : g.vals[src], in->P,
-                                                          shift, n_cta, g.cta_hist, digit_total, g.keys[dst],
-                                                          g.vals[dst]), GSR_LAUNCHED(1);
+  if (g_sort.load(std::memory_order_relaxed) == 1) {
+    GSR_LAUNCHED(os_sort_launch(g.keys, g.vals, in->P, g.cta_hist, stream));
     GSR_STAGE("depth_sort", in->debug, stream);
+  } else {
+    const int n_cta = (int)sort_ctas((size_t)in->P);
+    for (int pass = 0; pass < 4; pass++) {
+      const int src = pass & 1, dst = src ^ 1, shift = 8 * pass;
+      radix_hist_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], in->P, shift, n_cta, g.cta_hist);
+      uint32_t* digit_total = g.cta_hist + (size_t)256 * n_cta;
+      radix_rowscan_kernel<<<256, 256, 0, stream>>>(g.cta_hist, n_cta, digit_total);
+      radix_scatter_kernel<<<n_cta, RS_THREADS, 0, stream>>>(g.keys[src], pass == 0 ? nullptr : g.vals[src], in->P,
+                                                            shift, n_cta, g.cta_hist, digit_total, g.keys[dst],
+                                                            g.vals[dst]);
+      GSR_LAUNCHED(3);
+      GSR_STAGE("depth_sort", in->debug, stream);
+    }
   }
   }
   {
@@ -463,13 +472,18 @@ int gsr_backward_blend(const gsr_inputs* in, const void* geom, const void* binni
   if (R > 0) {
     ScopedStage prof_(GSR_STAGE_RENDER_BWD, stream);
     dim3 grid(cam.gx, cam.gy);
-    if (g_render_bwd.load(std::memory_order_relaxed) == 1)
+    const int variant = g_render_bwd.load(std::memory_order_relaxed);
+    if (variant == 1)
       render_bwd_kernel<<<grid, TILE_PIX, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0, g.g1, g.g2,
                                                        in->colors_precomp, im.final_T, im.n_contrib, dL_dpix, bw), GSR_LAUNCHED(1);
+    else if (variant == 3)
+      render_bwd2_kernel<true><<<grid, RB2_THREADS, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0,
+                                                                 g.g1, g.g2, in->colors_precomp, im.final_T,
+                                                                 im.n_contrib, dL_dpix, bw, bw.counters), GSR_LAUNCHED(1);
     else
-      render_bwd2_kernel<<<grid, RB2_THREADS, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0, g.g1,
-                                                           g.g2, in->colors_precomp, im.final_T, im.n_contrib,
-                                                           dL_dpix, bw), GSR_LAUNCHED(1);
+      render_bwd2_kernel<false><<<grid, RB2_THREADS, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0,
+                                                                  g.g1, g.g2, in->colors_precomp, im.final_T,
+                                                                  im.n_contrib, dL_dpix, bw, nullptr), GSR_LAUNCHED(1);
     GSR_STAGE("render_bwd", in->debug, stream);
   }
   return GSR_OK;
@@ -616,6 +630,40 @@ int gsr_sh_grad_from_factors(int32_t P, int32_t D, int32_t M, int32_t V, const f
     sh_grad_from_factors_kernel<false><<<blocks, PB_THREADS, 0, stream>>>(P, D, M, V, means3D, campos, factors,
                                                                          dL_dsh, accumulate), GSR_LAUNCHED(1);
   GSR_STAGE("sh_grad_from_factors", 0, stream);
+  return GSR_OK;
+}
+
+// ---- the depth sort on its own (tests, tools/sort_bench.py)
+int gsr_sort_scratch_bytes(int32_t n, size_t* bytes) {
+  if (n < 0 || !bytes) return fail(GSR_ERR_INVALID, "gsr_sort_scratch_bytes: bad arguments");
+  *bytes = align_up(4 * sort_scratch_words((size_t)n)) + ALIGN;
+  return GSR_OK;
+}
+
+int gsr_sort_pairs(int32_t n, uint32_t* keys, uint32_t* keys_tmp, uint32_t* vals, uint32_t* vals_tmp, void* scratch,
+                   int32_t variant, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n < 0) return fail(GSR_ERR_INVALID, "gsr_sort_pairs: n < 0");
+  if (n == 0) return GSR_OK;
+  if (!keys || !keys_tmp || !vals || !vals_tmp || !scratch) return fail(GSR_ERR_INVALID, "gsr_sort_pairs: NULL pointer");
+  uint32_t* k2[2] = {keys, keys_tmp};
+  uint32_t* v2[2] = {vals, vals_tmp};
+  if (variant == 1) {
+    GSR_LAUNCHED(os_sort_launch(k2, v2, n, (uint32_t*)scratch, stream));
+  } else {
+    uint32_t* cta_hist = (uint32_t*)scratch;
+    const int n_cta = (int)sort_ctas((size_t)n);
+    for (int pass = 0; pass < 4; pass++) {
+      const int src = pass & 1, dst = src ^ 1, shift = 8 * pass;
+      radix_hist_kernel<<<n_cta, RS_THREADS, 0, stream>>>(k2[src], n, shift, n_cta, cta_hist);
+      uint32_t* digit_total = cta_hist + (size_t)256 * n_cta;
+      radix_rowscan_kernel<<<256, 256, 0, stream>>>(cta_hist, n_cta, digit_total);
+      radix_scatter_kernel<<<n_cta, RS_THREADS, 0, stream>>>(k2[src], pass == 0 ? nullptr : v2[src], n, shift, n_cta,
+                                                            cta_hist, digit_total, k2[dst], v2[dst]);
+      GSR_LAUNCHED(3);
+    }
+  }
+  GSR_STAGE("sort_pairs", 0, stream);
   return GSR_OK;
 }
 

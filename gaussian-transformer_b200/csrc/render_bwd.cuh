@@ -277,11 +277,16 @@ __device__ __forceinline__ float rcp_approx(float x) {
   return y;
 }
 
-__global__ void __launch_bounds__(RB2_THREADS, 6) render_bwd2_kernel(
+// COUNT (test instantiation, option render_bwd = 3): additionally evaluates the forward's exact alpha (expf) and
+// counts, in counters[0..2], the accepted (pixel, Gaussian) pairs, the pairs the forward accepted but this kernel's
+// ex2.approx alpha rejects, and the reverse (defined deviation 4).
+template <bool COUNT>
+__global__ void __launch_bounds__(RB2_THREADS, COUNT ? 4 : 6) render_bwd2_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
     const float* __restrict__ bg, const float4* __restrict__ g0, const float4* __restrict__ g1,
     const float4* __restrict__ g2, const float* __restrict__ colors_precomp, const float* __restrict__ final_T,
-    const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix, BwdView acc) {
+    const uint32_t* __restrict__ n_contrib, const float* __restrict__ dL_dpix, BwdView acc,
+    unsigned long long* __restrict__ counters) {
   __shared__ StageRec s_rec[RENDER_BATCH];
   __shared__ float s_rba[RENDER_BATCH];
   __shared__ uint32_t s_id[RENDER_BATCH];
@@ -372,6 +377,21 @@ __global__ void __launch_bounds__(RB2_THREADS, 6) render_bwd2_kernel(
         // same acceptance as the forward (backward.cu:488-497)
         const bool v0 = (pos < lc0) && !(power.x > 0.0f) && !(al0 < 1.0f / 255.0f);
         const bool v1 = (pos < lc1) && !(power.y > 0.0f) && !(al1 < 1.0f / 255.0f);
+        if (COUNT) {
+          const float e0 = fminf(0.99f, __fmul_rn(b.y, expf(power.x))), e1 = fminf(0.99f, __fmul_rn(b.y, expf(power.y)));
+          const bool f0 = (pos < lc0) && !(power.x > 0.0f) && !(e0 < 1.0f / 255.0f);
+          const bool f1 = (pos < lc1) && !(power.y > 0.0f) && !(e1 < 1.0f / 255.0f);
+          const unsigned n_acc = __popc(__ballot_sync(0xffffffffu, f0)) + __popc(__ballot_sync(0xffffffffu, f1));
+          const unsigned n_lost = __popc(__ballot_sync(0xffffffffu, f0 && !v0)) +
+                                  __popc(__ballot_sync(0xffffffffu, f1 && !v1));
+          const unsigned n_extra = __popc(__ballot_sync(0xffffffffu, v0 && !f0)) +
+                                   __popc(__ballot_sync(0xffffffffu, v1 && !f1));
+          if (lane == 0) {
+            if (n_acc) atomicAdd(counters, (unsigned long long)n_acc);
+            if (n_lost) atomicAdd(counters + 1, (unsigned long long)n_lost);
+            if (n_extra) atomicAdd(counters + 2, (unsigned long long)n_extra);
+          }
+        }
         if (!__any_sync(0xffffffffu, v0 || v1)) continue;
         const float2 alpha = make_float2(v0 ? al0 : 0.f, v1 ? al1 : 0.f);
         const float2 Ge = make_float2(v0 ? G.x : 0.f, v1 ? G.y : 0.f);

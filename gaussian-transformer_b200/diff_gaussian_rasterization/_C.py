@@ -133,7 +133,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh,
                                  degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, sh_grad=True,
-                                 factor_sink=None, out=None, sh_rest=None):
+                                 factor_sink=None, out=None, sh_rest=None, debug_out=None):
     """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
 
     sh_grad=False (extension, used by gsr_dp): dL_dsh is not computed and returned as None; the caller rebuilds it
@@ -143,7 +143,8 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     geometry stage.  out (extension): {"means3D" | "sh" | "opacity" | "scales" | "rot": tensor} -- gradients written
     into the caller's tensors (same shape, float32, contiguous) instead of freshly allocated ones.  sh_rest
     (extension): split SH storage as in rasterize_gaussians; dL_dsh is then the pair (dL_dfeatures_dc (P,1,3),
-    dL_dfeatures_rest (P,M-1,3))."""
+    dL_dfeatures_rest (P,M-1,3)).  debug_out (test hook): a dict that receives "conic" = dL_dconic (P,2,2) and
+    "work" = the backward scratch buffer; nothing is retained otherwise."""
     _check_means(means3D)
     dev = means3D.device
     P = means3D.size(0)
@@ -213,7 +214,9 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
         for k in out:
             if g.get(k) is not None:
                 g[k].zero_()
-    rasterize_gaussians_backward.last_dL_dconic = g["conic"]  # exposed for the parity tests only
+    if debug_out is not None:
+        debug_out["conic"] = g["conic"]
+        debug_out["work"] = work if P != 0 else None
     g_sh = (g["sh"], g_rest) if split else g["sh"]
     return (g["means2D"], g["colors"], g["opacity"], g["means3D"], g["cov3D"], g_sh, g["scales"], g["rot"])
 

@@ -39,6 +39,7 @@ EXPORTS = (
     "gsr_backward_blend", "gsr_backward_geometry", "gsr_backward_sh_factors",
     "gsr_adam_step", "gsr_forward", "gsr_backward_geometry_split",
     "gsr_activate", "gsr_activate_backward", "gsr_densification_stats", "gsr_launch_count", "gsr_set_option",
+    "gsr_sort_scratch_bytes", "gsr_sort_pairs",
 )
 STAGES = ("preprocess_fwd", "depth_sort", "bin_count", "bin_scatter", "render_fwd", "render_bwd", "preprocess_bwd")
 
@@ -77,6 +78,8 @@ def load(path=LIB_PATH):
     lib.gsr_sh_color_factors.argtypes = [i32, vp, vp, vp, vp]
     lib.gsr_sh_grad_from_factors.argtypes = [i32, i32, i32, i32, vp, vp, vp, vp, i32, vp]
     lib.gsr_get_views.argtypes = [i32, i64, i32, i32, vp, vp, vp, ctypes.POINTER(gsr_views)]
+    lib.gsr_sort_scratch_bytes.argtypes = [i32, szp]
+    lib.gsr_sort_pairs.argtypes = [i32, vp, vp, vp, vp, vp, i32, vp]
     lib.gsr_launch_count.argtypes = [ctypes.c_int]
     lib.gsr_launch_count.restype = ctypes.c_int64
     lib.gsr_set_option.argtypes = [ctypes.c_char_p, i32]

@@ -8,7 +8,9 @@ the train.py:91-92 combination in ONE forward+backward pair of launches (csrc/lo
   becomes
     loss, Ll1 = l1_ssim_loss(image, gt_image, opt.lambda_dssim)
 
-CUDA float32 only; there is no CPU path.  The second image is the ground truth: it receives no gradient.
+CUDA float32 only; there is no CPU path.  Like the reference's functions, both arguments are differentiable
+(train_autoencoder.py:172 passes the network output SECOND): L1 and SSIM are symmetric in their arguments, so the
+gradient of the second image is the same kernel pair run with the roles swapped.
 """
 import ctypes
 
@@ -22,8 +24,6 @@ def _check(img, gt):
         raise RuntimeError("loss_utils: tensors must be CUDA tensors (there is no CPU path)")
     if img.shape != gt.shape or img.dim() not in (3, 4):
         raise RuntimeError("loss_utils: images must have the same (C,H,W) or (B,C,H,W) shape")
-    if gt.requires_grad:
-        raise RuntimeError("loss_utils: the second image is the ground truth and gets no gradient")
 
 
 def _forward(img, gt, lam):
@@ -58,16 +58,28 @@ class _L1SSIM(torch.autograd.Function):
         return out3
 
     @staticmethod
-    def backward(ctx, g_out):
-        x, y, scratch = ctx.saved_tensors
+    def _grad(x, y, lam, up, scratch):
+        """d loss / d x with `scratch` = the derivative maps of the forward pass over (x, y)."""
         C, H, W = x.shape
-        up = g_out.to(torch.float32).contiguous()[2:3]
         grad = torch.empty_like(x)
         with torch.cuda.device(x.device):
-            _lib.check(_lib.lib.gsr_l1_ssim_backward(C, H, W, x.data_ptr(), y.data_ptr(), float(ctx.lam), up.data_ptr(),
+            _lib.check(_lib.lib.gsr_l1_ssim_backward(C, H, W, x.data_ptr(), y.data_ptr(), float(lam), up.data_ptr(),
                                                      scratch.data_ptr(), grad.data_ptr(),
                                                      torch.cuda.current_stream(x.device).cuda_stream))
-        return grad.reshape(ctx.shape), None, None
+        return grad
+
+    @staticmethod
+    def backward(ctx, g_out):
+        x, y, scratch = ctx.saved_tensors
+        up = g_out.to(torch.float32).contiguous()[2:3]
+        gx = gy = None
+        if ctx.needs_input_grad[0]:
+            gx = _L1SSIM._grad(x, y, ctx.lam, up, scratch).reshape(ctx.shape)
+        if ctx.needs_input_grad[1]:
+            # the loss is symmetric: the second image's gradient is the first's with the roles swapped (its
+            # derivative maps come from one more forward pass over (y, x))
+            gy = _L1SSIM._grad(y, x, ctx.lam, up, _forward(y, x, ctx.lam)[1]).reshape(ctx.shape)
+        return gx, gy, None
 
 
 def l1_ssim_loss(image, gt_image, lambda_dssim=0.2):

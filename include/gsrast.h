@@ -258,6 +258,15 @@ typedef struct gsr_adam_group {
 GSR_API int gsr_adam_step(int32_t n_groups, const gsr_adam_group* groups, double beta1, double beta2, double eps,
                           void* stream);
 
+/* The depth sort of the forward on its own: stable ascending sort of n (uint32 key, uint32 value) pairs over all 32
+ * key bits; the values of the result are the ORIGINAL INDICES of the keys (vals on entry is ignored), i.e. the
+ * "value = Gaussian id" use of cub::DeviceRadixSort::SortPairs in DGR/cuda_rasterizer/rasterizer_impl.cu:300-308
+ * restricted to what the depth-ordered binning needs.  Result in keys / vals; keys_tmp / vals_tmp are ping-pong
+ * buffers of n words; scratch: gsr_sort_scratch_bytes(n).  variant: 1 = onesweep.cuh, 0 = depth_sort.cuh. */
+GSR_API int gsr_sort_scratch_bytes(int32_t n, size_t* bytes);
+GSR_API int gsr_sort_pairs(int32_t n, uint32_t* keys, uint32_t* keys_tmp, uint32_t* vals, uint32_t* vals_tmp,
+                           void* scratch, int32_t variant, void* stream);
+
 /* present[i] = (view-space z > 0.2).  Replaces Rasterizer::markVisible /
  * checkFrustum (DGR/cuda_rasterizer/rasterizer_impl.cu:54-66,141-153). */
 GSR_API int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix,
@@ -284,7 +293,9 @@ GSR_API int gsr_profile_enable(int on);
 GSR_API int64_t gsr_launch_count(int reset);
 /* Development / test switches (process-wide).  "bin_cta": -1 = pick the scatter kernel by list size (default),
  * 0 / 1 = force bin_pass_kernel<true> / bin_scatter_cta_kernel; "render_bwd": 2 = two pixels per thread (default),
- * 1 = one.  Initial values come from the environment variables GSR_BIN_CTA / GSR_RENDER_BWD, read once at load. */
+ * 1 = one, 3 = two + test counters (accepted pairs, and pairs whose accept/reject differs between the forward's expf
+ * and the backward's ex2.approx alpha, as three uint64 behind the accumulators of bwd_scratch).  "sort": 1 = onesweep depth sort (default), 0 = the histogram / row-scan / scatter
+ * sort.  Initial values come from the environment variables GSR_BIN_CTA / GSR_RENDER_BWD / GSR_SORT, read once at load. */
 GSR_API int gsr_set_option(const char* name, int32_t value);
 GSR_API int gsr_profile_read(float* ms /* [GSR_STAGE_COUNT] */, int32_t* counts /* [GSR_STAGE_COUNT] */);
 

@@ -346,3 +346,82 @@ def test_sh_degree_growth_uses_stride_M():
                           shs=d["sh"], scales=d["scales"], rotations=d["rotations"])
         imgs.append(c)
     assert not torch.equal(imgs[0], imgs[3])
+
+
+def _render_leaves(d, **kw):
+    m3, sh, op, scl, rot = (_leaf(d[k]) for k in ("means3D", "sh", "opacities", "scales", "rotations"))
+    color, radii = _module(d, **kw)(means3D=m3, means2D=torch.zeros_like(m3), opacities=op, shs=sh, scales=scl,
+                                    rotations=rot)
+    return color, radii, (m3, sh, op, scl, rot)
+
+
+def test_prefiltered_violation_raises():
+    """prefiltered=True promises that no point is behind the near plane; the reference prints and __trap()s the
+    kernel (auxiliary.h:154-162), which surfaces as a CUDA error = RuntimeError.  Here the forward raises
+    RuntimeError after the kernel flagged the violation (defined deviation 3), and a scene
+    that keeps the promise renders the same bits with and without the flag."""
+    sc = S.scene_S(2000, 160, 96, seed=21)  # 2 % of the points sit behind the near plane
+    d = to_device(sc)
+    with pytest.raises(RuntimeError, match="point is filtered although prefiltered is set"):
+        _render_leaves(d, prefiltered=True)
+    keep = sc["means3D"][:, 2] > 0.5
+    for k in ("means3D", "sh", "opacities", "scales", "rotations"):
+        sc[k] = np.ascontiguousarray(sc[k][keep])
+    sc["P"] = int(keep.sum())
+    d = to_device(sc)
+    c0, r0, _ = _render_leaves(d, prefiltered=False)
+    c1, r1, _ = _render_leaves(d, prefiltered=True)
+    assert torch.equal(c0, c1) and torch.equal(r0, r1)
+
+
+def test_debug_snapshots_on_failure(tmp_path, monkeypatch):
+    """debug=True contract of DGR/diff_gaussian_rasterization/__init__.py:83-90,132-139: when the native call fails,
+    the argument tuple is written to snapshot_fw.dump / snapshot_bw.dump in the working directory and the error is
+    re-raised; the dumps replay through the _C-shaped entry points.  Without debug nothing is written."""
+    from diff_gaussian_rasterization import _C
+    monkeypatch.chdir(tmp_path)
+    sc = S.scene_S(1500, 160, 96, seed=22)
+    d = to_device(sc)
+    # forward failure: a genuine one (prefiltered violation detected by the kernel)
+    with pytest.raises(RuntimeError):
+        _render_leaves(d, prefiltered=True, debug=False)
+    assert not (tmp_path / "snapshot_fw.dump").exists()
+    with pytest.raises(RuntimeError):
+        _render_leaves(d, prefiltered=True, debug=True)
+    fw = torch.load(tmp_path / "snapshot_fw.dump", weights_only=False)
+    assert len(fw) == 19 and fw[1].shape == (1500, 3) and fw[17] is True and fw[18] is True
+    args = [a.cuda() if isinstance(a, torch.Tensor) else a for a in fw]
+    args[17] = False  # the same tuple with the promise withdrawn replays through the pybind-shaped entry
+    R, color, radii, *_ = _C.rasterize_gaussians(*args)
+    c_ok, r_ok, _ = _render_leaves(d)
+    assert R > 0 and torch.equal(color, c_ok.detach()) and torch.equal(radii, r_ok)
+    # backward failure: the native backward is made to fail (an invalid library status)
+    color, radii, leaves = _render_leaves(d, debug=True)
+    real = _C.rasterize_gaussians_backward
+
+    def failing(*a, **k):
+        raise RuntimeError("gsrast: forced failure")
+    monkeypatch.setattr(_C, "rasterize_gaussians_backward", failing)
+    with pytest.raises(RuntimeError, match="forced failure"):
+        color.sum().backward()
+    monkeypatch.setattr(_C, "rasterize_gaussians_backward", real)
+    bw = torch.load(tmp_path / "snapshot_bw.dump", weights_only=False)
+    assert len(bw) == 21 and bw[2].dtype == torch.int32 and bw[12].shape == color.shape
+    args = [a.cuda() if isinstance(a, torch.Tensor) else a for a in bw]
+    grads = real(*args)  # (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drot)
+    color2, _, leaves2 = _render_leaves(d)
+    color2.sum().backward()
+    assert rel_err(np_(grads[3]), np_(leaves2[0].grad)) <= 1e-3 and rel_err(np_(grads[5]), np_(leaves2[1].grad)) <= 1e-3
+
+
+def test_launch_counter_counts_kernels():
+    from diff_gaussian_rasterization import _lib
+    sc = S.scene_S(1500, 160, 96, seed=23)
+    d = to_device(sc)
+    _lib.launch_count(reset=True)
+    color, _, _ = _render_leaves(d)
+    n_fwd = _lib.launch_count()
+    color.sum().backward()
+    n_all = _lib.launch_count(reset=True)
+    assert 4 <= n_fwd <= 24 and n_fwd + 2 <= n_all <= n_fwd + 4, (n_fwd, n_all)
+    assert _lib.launch_count() == 0

@@ -128,3 +128,33 @@ def test_1080p_vs_torch():
     err = (a.grad - c.grad).abs().max().item()
     assert err <= GRAD_TOL * gmax
     assert err <= 1.25 * (b.grad - c.grad).abs().max().item()   # no farther from fp64 than the reference formula
+
+
+def test_second_argument_is_differentiable_like_the_reference():
+    """train_autoencoder.py:172 calls ssim(in_im, out_im) with the network output SECOND; the reference's functions
+    are differentiable in both arguments.  Checked against the torch fp32 restatement's autograd: gradient of the
+    second image alone, and of both images at once."""
+    from utils.loss_utils import l1_loss, l1_ssim_loss, ssim
+    g = torch.Generator().manual_seed(5)
+    a = torch.rand(3, 70, 90, generator=g).cuda()
+    b = (a + 0.2 * torch.rand(3, 70, 90, generator=g).cuda()).clamp(0, 1)
+    for both in (False, True):
+        x = a.clone().requires_grad_(both)
+        y = b.clone().requires_grad_(True)
+        (1.0 - ssim(x, y)).backward()
+        xr = a.clone().requires_grad_(both)
+        yr = b.clone().requires_grad_(True)
+        _, _, s_ref = _torch_loss(xr[None], yr[None], 0.2)
+        (1.0 - s_ref).backward()
+        assert (y.grad - yr.grad).abs().max() <= 2 * GRAD_TOL * yr.grad.abs().max()
+        if both:
+            assert (x.grad - xr.grad).abs().max() <= 2 * GRAD_TOL * xr.grad.abs().max()
+    y = b.clone().requires_grad_(True)
+    l1_loss(a, y).backward()
+    assert torch.equal(y.grad, torch.sign(b - a) / a.numel())
+    y.grad = None
+    loss, _ = l1_ssim_loss(a, y, 0.2)
+    loss.backward()
+    yr = b.clone().requires_grad_(True)
+    _torch_loss(a[None], yr[None], 0.2)[0].backward()
+    assert (y.grad - yr.grad).abs().max() <= 2 * GRAD_TOL * yr.grad.abs().max()

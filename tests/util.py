@@ -64,7 +64,7 @@ def ours_forward(d, colors_precomp=None, cov3D_precomp=None, debug=False):
     return out
 
 
-def ours_backward(d, fwd, dL_dpix, colors_precomp=None, cov3D_precomp=None, debug=False):
+def ours_backward(d, fwd, dL_dpix, colors_precomp=None, cov3D_precomp=None, debug=False, dbg=None):
     from diff_gaussian_rasterization import _C
     empty = torch.Tensor([])
     use_sh = colors_precomp is None
@@ -74,11 +74,11 @@ def ours_backward(d, fwd, dL_dpix, colors_precomp=None, cov3D_precomp=None, debu
         d["scales"] if cov3D_precomp is None else empty, d["rotations"] if cov3D_precomp is None else empty,
         d["scale_modifier"], empty if cov3D_precomp is None else cov3D_precomp, d["viewmatrix"], d["projmatrix"],
         d["tanfovx"], d["tanfovy"], dL_dpix, d["sh"] if use_sh else empty, d["sh_degree"], d["campos"], geom,
-        fwd["num_rendered"], binning, img, debug)
+        fwd["num_rendered"], binning, img, debug, debug_out=(dbg := {} if dbg is None else dbg))
     torch.cuda.synchronize()
     names = ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rot")
     g = dict(zip(names, r))
-    g["conic"] = _C.rasterize_gaussians_backward.last_dL_dconic.view(-1, 4)
+    g["conic"] = dbg["conic"].view(-1, 4)
     return g
 
 
