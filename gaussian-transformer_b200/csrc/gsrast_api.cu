@@ -290,16 +290,27 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   const int blocks = (in->P + 255) / 256;
   {
   ScopedStage prof_(GSR_STAGE_PREPROCESS_FWD, stream);
-  if (vec_sh)
-    preprocess_fwd_kernel<true><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
-                                                            in->rotations, in->opacities, in->sh, nullptr,
-                                                            in->colors_precomp, in->cov3D_precomp, cam,
-                                                            in->prefiltered, radii, g, im.ctrl), GSR_LAUNCHED(1);
-  else
-    preprocess_fwd_kernel<false><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,
-                                                             in->rotations, in->opacities, in->sh, sh_rest,
-                                                             in->colors_precomp, in->cov3D_precomp, cam,
-                                                             in->prefiltered, radii, g, im.ctrl), GSR_LAUNCHED(1);
+  const bool stage_in = aligned16(in->means3D) && (!in->scales || aligned16(in->scales));
+  const bool staged_sh = in->sh && !sh_rest && !in->colors_precomp && (in->M == 16 || in->M == 4) && aligned16(in->sh);
+#define GSR_PF_LAUNCH(VEC, STG)                                                                                    \
+  preprocess_fwd_kernel<VEC, STG><<<blocks, 256, 0, stream>>>(in->P, in->D, in->M, in->means3D, in->scales,       \
+                                                               in->rotations, in->opacities, in->sh,               \
+                                                               VEC ? nullptr : sh_rest, in->colors_precomp,        \
+                                                               in->cov3D_precomp, cam, in->prefiltered, radii, g,  \
+                                                               im.ctrl)
+#define GSR_PFS_LAUNCH(MT, STG)                                                                                     \
+  preprocess_fwd_staged_kernel<MT, STG><<<(in->P + PF_THREADS - 1) / PF_THREADS, PF_THREADS, 0, stream>>>(         \
+      in->P, in->D, in->means3D, in->scales, in->rotations, in->opacities, in->sh, in->cov3D_precomp, cam,         \
+      in->prefiltered, radii, g, im.ctrl)
+  if (staged_sh && in->M == 16) { if (stage_in) GSR_PFS_LAUNCH(16, true); else GSR_PFS_LAUNCH(16, false); }
+  else if (staged_sh) { if (stage_in) GSR_PFS_LAUNCH(4, true); else GSR_PFS_LAUNCH(4, false); }
+  else if (vec_sh && stage_in) GSR_PF_LAUNCH(true, true);
+  else if (vec_sh) GSR_PF_LAUNCH(true, false);
+  else if (stage_in) GSR_PF_LAUNCH(false, true);
+  else GSR_PF_LAUNCH(false, false);
+#undef GSR_PF_LAUNCH
+#undef GSR_PFS_LAUNCH
+  GSR_LAUNCHED(1);
   GSR_STAGE("preprocess_fwd", in->debug, stream);
   }
   // depth sort of the P Gaussians: 4 stable 8-bit passes, result in keys[0] / vals[0]

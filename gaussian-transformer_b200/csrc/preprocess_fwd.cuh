@@ -168,65 +168,132 @@ __device__ __forceinline__ void sh_to_rgb(int deg, int M, const float* __restric
   b = bb < 0.f ? 0.f : bb;
 }
 
-template <bool VEC_SH>
+// Geometry half of preprocessCUDA for one Gaussian (forward.cu:182-237 without the colour): cull, projection, cov3D,
+// EWA cov2D, conic, radius, tile rectangle.  Returns false when the Gaussian is culled; otherwise o0 = (mean2D.x,
+// mean2D.y, depth, radius bits), conic = (A, B, C), tiles = rectangle area.  Every fp32 operation on the way to an
+// integer result is an explicit round-to-nearest intrinsic placed where the reference's compiled code rounds.
+__device__ __forceinline__ bool pre_geometry(int i, float px3, float py3, float pz3, float s0, float s1, float s2,
+                                             float4 q, const float* __restrict__ cov3D_precomp, const Cam& cam,
+                                             int prefiltered, uint32_t* __restrict__ ctrl, float4& o0, float& conx,
+                                             float& cony, float& conz, int& radius, int& tiles) {
+  const float* __restrict__ view = cam.view;
+  const float* __restrict__ proj = cam.proj;
+  // in_frustum: cull iff p_view.z <= 0.2 (NaN passes, like the reference)
+  const float vz = xf_row(view, 2, px3, py3, pz3);
+  if (vz <= 0.2f) {
+    if (prefiltered) atomicOr(&ctrl[CTRL_FLAGS], 1u);
+    return false;
+  }
+  const float hw = xf_row(proj, 3, px3, py3, pz3);
+  const float hx = xf_row(proj, 0, px3, py3, pz3);
+  const float hy = xf_row(proj, 1, px3, py3, pz3);
+  const float pw = __frcp_rn(__fadd_rn(hw, 0.0000001f));
+  const float projx = __fmul_rn(hx, pw), projy = __fmul_rn(hy, pw);
+  float c3[6];
+  if (cov3D_precomp != nullptr) {
+#pragma unroll
+    for (int k = 0; k < 6; k++) c3[k] = __ldg(cov3D_precomp + 6 * (size_t)i + k);
+  } else {
+    cov3d_from_scale_rot(s0, s1, s2, cam.scale_modifier, q.x, q.y, q.z, q.w, c3);
+  }
+  const float tx = xf_row(view, 0, px3, py3, pz3);
+  const float ty = xf_row(view, 1, px3, py3, pz3);
+  float a, b, c;
+  cov2d(tx, ty, vz, cam, c3, view, a, b, c);
+  const float det = __fmaf_rn(a, c, -__fmul_rn(b, b));
+  if (det == 0.0f) return false;
+  const float det_inv = __frcp_rn(det);
+  conx = __fmul_rn(c, det_inv); cony = __fmul_rn(b, -det_inv); conz = __fmul_rn(a, det_inv);
+  const float mid = __fmul_rn(__fadd_rn(a, c), 0.5f);
+  const float disc = fmaxf(__fmaf_rn(mid, mid, -det), 0.1f);
+  const float sq = __fsqrt_rn(disc);
+  const float lmax = fmaxf(__fadd_rn(mid, sq), __fsub_rn(mid, sq));
+  const int my_radius = __float2int_rz(ceilf(__fmul_rn(__fsqrt_rn(lmax), 3.0f)));
+  // lambda_max >= 0.3 for finite input, so radius >= 2; radius 0 only arises from a NaN covariance.  The
+  // reference then still counts the Gaussian's tile but never writes its sort key (duplicateWithKeys skips
+  // radii <= 0, rasterizer_impl.cu:84), i.e. it renders an uninitialised key.  Defined behaviour here: culled.
+  if (my_radius <= 0) return false;
+  const float mx = ndc2pix(projx, cam.W), my = ndc2pix(projy, cam.H);
+  int minx, miny, maxx, maxy;
+  get_rect(mx, my, my_radius, cam.gx, cam.gy, minx, miny, maxx, maxy);
+  tiles = (maxx - minx) * (maxy - miny);
+  if (tiles == 0) return false;
+  radius = my_radius;
+  o0 = make_float4(mx, my, vz, __int_as_float(my_radius));
+  return true;
+}
+
+constexpr int PF_THREADS = 128;
+#ifndef GSR_PF_MIN_CTAS
+#define GSR_PF_MIN_CTAS 7
+#endif
+#ifndef GSR_PF_EARLY_SH
+#define GSR_PF_EARLY_SH 1
+#endif
+
+// Loads of the 12-byte rows of means3D / scales of the CTA's Gaussians: one contiguous block each, moved with
+// coalesced 128-bit loads into shared memory (STAGE_IN: both arrays 16-byte aligned; stride-3 reads are conflict
+// free); else plain per-thread loads.
+template <bool STAGE_IN, int THREADS>
+__device__ __forceinline__ void load_mean_scale(int P, int base, int tid, const float* __restrict__ means3D,
+                                                const float* __restrict__ scales, float* s_mean, float* s_scale,
+                                                float* m, float* sc) {
+  const int i = base + tid;
+  if (STAGE_IN) {
+    const int nfl = min(THREADS, P - base) * 3;
+    const float4* __restrict__ m4 = reinterpret_cast<const float4*>(means3D + (size_t)base * 3);
+    const float4* __restrict__ s4 = reinterpret_cast<const float4*>(scales + (size_t)base * 3);
+    if (tid < (nfl >> 2)) {
+      reinterpret_cast<float4*>(s_mean)[tid] = __ldg(m4 + tid);
+      if (scales != nullptr) reinterpret_cast<float4*>(s_scale)[tid] = __ldg(s4 + tid);
+    } else if (tid < (nfl >> 2) + (nfl & 3)) {  // the last CTA's 1..3 trailing floats
+      const int j = ((nfl >> 2) << 2) + tid - (nfl >> 2);
+      s_mean[j] = __ldg(means3D + (size_t)base * 3 + j);
+      if (scales != nullptr) s_scale[j] = __ldg(scales + (size_t)base * 3 + j);
+    }
+    __syncthreads();
+    if (i < P) {
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        m[k] = s_mean[3 * tid + k];
+        sc[k] = scales != nullptr ? s_scale[3 * tid + k] : 0.f;
+      }
+    }
+  } else if (i < P) {
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      m[k] = __ldg(means3D + 3 * (size_t)i + k);
+      sc[k] = scales != nullptr ? __ldg(scales + 3 * (size_t)i + k) : 0.f;
+    }
+  }
+}
+
+// Generic kernel: any M / alignment, colours precomputed, split SH storage.  One thread per Gaussian; coefficient rows
+// are read straight from global memory (VEC_SH: as float4).
+template <bool VEC_SH, bool STAGE_IN>
 __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
     int P, int D, int M, const float* __restrict__ means3D, const float* __restrict__ scales,
     const float* __restrict__ rotations, const float* __restrict__ opacities, const float* __restrict__ shs,
     const float* __restrict__ sh_rest, const float* __restrict__ colors_precomp,
     const float* __restrict__ cov3D_precomp, Cam cam, int prefiltered,
     int* __restrict__ radii, GeomView geom, uint32_t* __restrict__ ctrl) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  __shared__ __align__(16) float s_mean[STAGE_IN ? 256 * 3 : 4], s_scale[STAGE_IN ? 256 * 3 : 4];
+  const int tid = threadIdx.x, base = blockIdx.x * 256;
+  const int i = base + tid;
+  float4 q_in = make_float4(0.f, 0.f, 0.f, 0.f);
+  float opac_in = 0.f;
+  if (i < P) {  // issued before anything waits: one DRAM round trip for all per-Gaussian inputs
+    if (rotations != nullptr) q_in = __ldg(reinterpret_cast<const float4*>(rotations) + i);
+    opac_in = __ldg(opacities + i);
+  }
+  float m[3] = {0.f, 0.f, 0.f}, sc[3] = {0.f, 0.f, 0.f};
+  load_mean_scale<STAGE_IN, 256>(P, base, tid, means3D, scales, s_mean, s_scale, m, sc);
   if (i >= P) return;
-  int out_radius = 0;
+  int out_radius = 0, tiles = 0;
   float4 o0 = make_float4(0.f, 0.f, 0.f, 0.f), o1 = o0, o2 = o0;
-  do {
-    const float px3 = __ldg(means3D + 3 * (size_t)i), py3 = __ldg(means3D + 3 * (size_t)i + 1),
-                pz3 = __ldg(means3D + 3 * (size_t)i + 2);
-    const float* __restrict__ view = cam.view;
-    const float* __restrict__ proj = cam.proj;
-    // in_frustum: cull iff p_view.z <= 0.2 (NaN passes, like the reference)
-    const float vz = xf_row(view, 2, px3, py3, pz3);
-    if (vz <= 0.2f) {
-      if (prefiltered) atomicOr(&ctrl[CTRL_FLAGS], 1u);
-      break;
-    }
-    const float hw = xf_row(proj, 3, px3, py3, pz3);
-    const float hx = xf_row(proj, 0, px3, py3, pz3);
-    const float hy = xf_row(proj, 1, px3, py3, pz3);
-    const float pw = __frcp_rn(__fadd_rn(hw, 0.0000001f));
-    const float projx = __fmul_rn(hx, pw), projy = __fmul_rn(hy, pw);
-    float c3[6];
-    if (cov3D_precomp != nullptr) {
-#pragma unroll
-      for (int k = 0; k < 6; k++) c3[k] = __ldg(cov3D_precomp + 6 * (size_t)i + k);
-    } else {
-      const float s0 = __ldg(scales + 3 * (size_t)i), s1 = __ldg(scales + 3 * (size_t)i + 1),
-                  s2 = __ldg(scales + 3 * (size_t)i + 2);
-      const float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + i);
-      cov3d_from_scale_rot(s0, s1, s2, cam.scale_modifier, q.x, q.y, q.z, q.w, c3);
-    }
-    const float tx = xf_row(view, 0, px3, py3, pz3);
-    const float ty = xf_row(view, 1, px3, py3, pz3);
-    float a, b, c;
-    cov2d(tx, ty, vz, cam, c3, view, a, b, c);
-    const float det = __fmaf_rn(a, c, -__fmul_rn(b, b));
-    if (det == 0.0f) break;
-    const float det_inv = __frcp_rn(det);
-    const float conx = __fmul_rn(c, det_inv), cony = __fmul_rn(b, -det_inv), conz = __fmul_rn(a, det_inv);
-    const float mid = __fmul_rn(__fadd_rn(a, c), 0.5f);
-    const float disc = fmaxf(__fmaf_rn(mid, mid, -det), 0.1f);
-    const float sq = __fsqrt_rn(disc);
-    const float lmax = fmaxf(__fadd_rn(mid, sq), __fsub_rn(mid, sq));
-    const int my_radius = __float2int_rz(ceilf(__fmul_rn(__fsqrt_rn(lmax), 3.0f)));
-    // lambda_max >= 0.3 for finite input, so radius >= 2; radius 0 only arises from a NaN covariance.  The
-    // reference then still counts the Gaussian's tile but never writes its sort key (duplicateWithKeys skips
-    // radii <= 0, rasterizer_impl.cu:84), i.e. it renders an uninitialised key.  Defined behaviour here: culled.
-    if (my_radius <= 0) break;
-    const float mx = ndc2pix(projx, cam.W), my = ndc2pix(projy, cam.H);
-    int minx, miny, maxx, maxy;
-    get_rect(mx, my, my_radius, cam.gx, cam.gy, minx, miny, maxx, maxy);
-    const int tiles = (maxx - minx) * (maxy - miny);
-    if (tiles == 0) break;
+  float conx, cony, conz;
+  if (pre_geometry(i, m[0], m[1], m[2], sc[0], sc[1], sc[2], q_in, cov3D_precomp, cam, prefiltered, ctrl, o0, conx,
+                   cony, conz, out_radius, tiles)) {
     float r, g, bl;
     uint32_t clamped = 0;
     if (colors_precomp != nullptr) {
@@ -234,19 +301,122 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
       g = __ldg(colors_precomp + 3 * (size_t)i + 1);
       bl = __ldg(colors_precomp + 3 * (size_t)i + 2);
     } else {
-      const float dx = px3 - __ldg(cam.campos), dy = py3 - __ldg(cam.campos + 1), dz = pz3 - __ldg(cam.campos + 2);
+      const float dx = m[0] - __ldg(cam.campos), dy = m[1] - __ldg(cam.campos + 1), dz = m[2] - __ldg(cam.campos + 2);
       if (sh_rest != nullptr)
         sh_to_rgb<false>(D, M, shs + (size_t)i * 3, sh_rest + (size_t)i * (M - 1) * 3, dx, dy, dz, r, g, bl, clamped);
       else
         sh_to_rgb<VEC_SH>(D, M, shs + (size_t)i * M * 3, nullptr, dx, dy, dz, r, g, bl, clamped);
     }
-    out_radius = my_radius;
-    o0 = make_float4(mx, my, vz, __int_as_float(my_radius));
-    o1 = make_float4(conx, cony, conz, __ldg(opacities + i));
+    o1 = make_float4(conx, cony, conz, opac_in);
     o2 = make_float4(r, g, bl, __uint_as_float(((uint32_t)tiles << 3) | clamped));
-  } while (0);
+  } else {
+    out_radius = 0;
+    o0 = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
   radii[i] = out_radius;
-  geom.keys[0][i] = out_radius > 0 ? __float_as_uint(o0.z) : 0xffffffffu;  // depth-sort key (depth_sort.cuh)
+  geom.keys[0][i] = out_radius > 0 ? __float_as_uint(o0.z) : 0xffffffffu;  // depth-sort key
+  geom.g0[i] = o0;
+  geom.g1[i] = o1;
+  geom.g2[i] = o2;
+}
+
+// Main kernel: SH rows of MT coefficients (MT = 16 or 4) in one 16-byte aligned (P, MT, 3) array.  A CTA owns 128
+// consecutive Gaussians.  The geometry half runs first; the coefficient rows of the Gaussians that survived it --
+// contiguous in global memory -- are then copied into shared memory with COALESCED 16-byte asynchronous copies
+// (LDGSTS), 8 lanes per 128-byte line, into rows padded to an odd number of float4 so that every thread reads its own
+// row without bank conflicts.  (One thread reading its 192-byte row straight from global memory costs 32 L1
+// wavefronts per load instruction: at 1 M Gaussians the L1 data pipe was 59 % busy for the whole kernel and bounded
+// it at 3.4 TB/s.)
+template <int MT, bool STAGE_IN>
+__global__ void __launch_bounds__(PF_THREADS, GSR_PF_MIN_CTAS) preprocess_fwd_staged_kernel(
+    int P, int D, const float* __restrict__ means3D, const float* __restrict__ scales,
+    const float* __restrict__ rotations, const float* __restrict__ opacities, const float* __restrict__ shs,
+    const float* __restrict__ cov3D_precomp, Cam cam, int prefiltered, int* __restrict__ radii, GeomView geom,
+    uint32_t* __restrict__ ctrl) {
+  constexpr int NF = 3 * MT, F4 = NF / 4, RS4 = F4 | 1;
+  __shared__ float4 s_tile[PF_THREADS * RS4];
+  __shared__ __align__(16) float s_mean[STAGE_IN ? PF_THREADS * 3 : 4], s_scale[STAGE_IN ? PF_THREADS * 3 : 4];
+  __shared__ uint32_t s_vis[PF_THREADS / 32];
+  const int tid = threadIdx.x, base = blockIdx.x * PF_THREADS;
+  const int i = base + tid;
+  const int nG = min(PF_THREADS, P - base);
+  float4 q_in = make_float4(0.f, 0.f, 0.f, 0.f);
+  float opac_in = 0.f;
+  if (i < P) {
+    if (rotations != nullptr) q_in = __ldg(reinterpret_cast<const float4*>(rotations) + i);
+    opac_in = __ldg(opacities + i);
+  }
+  // chunks (float4) of a row that hold the (D+1)^2 active coefficients
+  const int K = (D + 1) * (D + 1), c4 = (3 * K + 3) >> 2;
+  auto issue_sh_copies = [&](bool only_visible) {
+    const uint32_t tile_addr = (uint32_t)__cvta_generic_to_shared(s_tile);
+    const float4* __restrict__ src4 = reinterpret_cast<const float4*>(shs + (size_t)base * NF);
+#pragma unroll 4
+    for (int j = tid; j < nG * F4; j += PF_THREADS) {
+      const int row = j / F4, col = j - row * F4;
+      if (col < c4 && (!only_visible || ((s_vis[row >> 5] >> (row & 31)) & 1u)))
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(tile_addr + (uint32_t)(row * RS4 + col) * 16u),
+                     "l"(src4 + j)
+                     : "memory");
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+#if GSR_PF_EARLY_SH
+  // The rows of ALL the CTA's Gaussians are requested before the geometry runs, so that the copy overlaps it (the
+  // price: the rows of the culled ones, 14 % at config 2).
+  issue_sh_copies(false);
+#endif
+  float m[3] = {0.f, 0.f, 0.f}, sc[3] = {0.f, 0.f, 0.f};
+  load_mean_scale<STAGE_IN, PF_THREADS>(P, base, tid, means3D, scales, s_mean, s_scale, m, sc);
+  int out_radius = 0, tiles = 0;
+  float4 o0 = make_float4(0.f, 0.f, 0.f, 0.f), o1 = o0, o2 = o0;
+  float conx = 0.f, cony = 0.f, conz = 0.f;
+  bool visible = false;
+  if (i < P)
+    visible = pre_geometry(i, m[0], m[1], m[2], sc[0], sc[1], sc[2], q_in, cov3D_precomp, cam, prefiltered, ctrl, o0,
+                           conx, cony, conz, out_radius, tiles);
+  const unsigned vm = __ballot_sync(0xffffffffu, visible);
+  if ((tid & 31) == 0) s_vis[tid >> 5] = vm;
+  __syncthreads();
+#if !GSR_PF_EARLY_SH
+  issue_sh_copies(true);
+#endif
+  asm volatile("cp.async.wait_all;" ::: "memory");
+  __syncthreads();
+  if (i >= P) return;
+  if (visible) {
+    const float dx = m[0] - __ldg(cam.campos), dy = m[1] - __ldg(cam.campos + 1), dz = m[2] - __ldg(cam.campos + 2);
+    const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+    float basis[16];
+    sh_basis(D, dx / len, dy / len, dz / len, basis);
+    const float4* row4 = s_tile + tid * RS4;
+    float acc[3] = {0.f, 0.f, 0.f};
+    // chunk by chunk (float j of the row belongs to coefficient j / 3, channel j % 3; same accumulation order per
+    // channel as forward.cu:30-61), so that only one float4 of the row is live at a time
+#pragma unroll
+    for (int k4 = 0; k4 < F4; k4++) {
+      if (k4 < c4) {
+        const float4 v = row4[k4];
+        const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          const int j = 4 * k4 + u;
+          if (j / 3 < K) acc[j % 3] = fmaf(basis[j / 3], e[u], acc[j % 3]);
+        }
+      }
+    }
+    const float rr = acc[0] + 0.5f, gg = acc[1] + 0.5f, bb = acc[2] + 0.5f;
+    const uint32_t clamped = (rr < 0.f ? 1u : 0u) | (gg < 0.f ? 2u : 0u) | (bb < 0.f ? 4u : 0u);
+    // glm::max(x, 0) is (x < 0) ? 0 : x, so a NaN colour stays NaN (forward.cu:70)
+    o1 = make_float4(conx, cony, conz, opac_in);
+    o2 = make_float4(rr < 0.f ? 0.f : rr, gg < 0.f ? 0.f : gg, bb < 0.f ? 0.f : bb,
+                     __uint_as_float(((uint32_t)tiles << 3) | clamped));
+  } else {
+    out_radius = 0;
+    o0 = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  radii[i] = out_radius;
+  geom.keys[0][i] = out_radius > 0 ? __float_as_uint(o0.z) : 0xffffffffu;  // depth-sort key (onesweep.cuh)
   geom.g0[i] = o0;
   geom.g1[i] = o1;
   geom.g2[i] = o2;
