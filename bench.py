@@ -25,6 +25,7 @@ sys.path[:0] = [os.path.join(ROOT, "gaussian-transformer_b200"), os.path.join(RO
 
 P_GAUSS, WIDTH, HEIGHT, SH_DEG, M_COEF = 1_000_000, 1920, 1080, 3, 16
 METRIC = "fwd+bwd iters/s (rasterize_gaussians, 1M Gaussians SH3, 1920x1080)"
+WORKLOAD = "C2: scene S (seed 0), 1M Gaussians, SH degree 3, 1920x1080, 1 view per GPU, fwd+bwd"
 UNIT = "iters/s"
 TENSORS = ("means3D", "scales", "rotations", "opacities", "sh", "bg", "viewmatrix", "projmatrix", "campos")
 LEAVES = ("means3D", "sh", "opacities", "scales", "rotations")
@@ -37,10 +38,17 @@ def parse():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the ~10-20 s CPU oracle timing")
+    ap.add_argument("--no-c3", action="store_true", help="N > 1: skip the C3 (3M Gaussians, 8-view batch) record")
     ap.add_argument("--timeline", default=None, help="dev: write a kernel timeline of 2 steps (torch.profiler) and exit")
-    ap.add_argument("--dp-exchange", default="factors", choices=("factors", "allreduce"),
-                    help="N > 1: all-gather 12 B/Gaussian SH factors + all-reduce 44 B/Gaussian (default), or "
-                         "all-reduce the full 236 B/Gaussian")
+    ap.add_argument("--dp-exchange", default="peer", choices=("peer", "factors", "allreduce"),
+                    help="N > 1: our kernels over NVLink peer memory (default: fused factor gather + SH rebuild, "
+                         "two-shot all-reduce of 44 B/Gaussian), the same exchange with NCCL (all-gather of 12 "
+                         "B/Gaussian/view SH factors + all-reduce of 44 B/Gaussian), or one NCCL all-reduce of the "
+                         "full 236 B/Gaussian")
+    ap.add_argument("--peer-gather", default="nccl", choices=("nccl", "copy", "fused"),
+                    help="peer exchange: how the SH-factor records travel (gsr_dp.PeerExchange)")
+    ap.add_argument("--no-multimem", action="store_true", help="peer exchange: two-shot P2P kernel even where the "
+                                                                "allocation has an NVSwitch multicast mapping")
     return ap.parse_args()
 
 
@@ -52,7 +60,7 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+    """nvidia-smi clocks / throttle reasons sampled every 20 ms while the timed region runs."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -61,7 +69,7 @@ class ClockSampler:
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         try:
             self.p = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                       "--format=csv,noheader,nounits", "-lms", "50"], stdout=self.f,
+                                       "--format=csv,noheader,nounits", "-lms", "20"], stdout=self.f,
                                       stderr=subprocess.DEVNULL)
         except Exception:
             self.p = None
@@ -110,14 +118,15 @@ def algorithmic_bytes(P, V, R, N, K, M):
     return a_fwd + a_bwd, per_stage
 
 
-# dram__bytes_read.sum + dram__bytes_write.sum per launch on the C2 workload, from the `ncu --set full` capture
-# summarised in profiles/r01_ncu_full_metrics.txt (a property of the workload, not of the run: bench.py only ever
-# runs C2).  Below the algorithmic bytes wherever list entries and per-Gaussian records are re-read from the L2.
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the `ncu --set full` capture of the yaw-0 C2 view
+# (V = 860,991, R = 12,071,224) summarised in profiles/r02_ncu_full_metrics.txt.  Quoted as roofline.traffic only when
+# the run's own V and R equal the capture's (N = 1); otherwise traffic is null.
+NCU_CAPTURE = {"V": 860991, "R": 12071224, "source": "profiles/r02_ncu_full_metrics.txt"}
 NCU_DRAM_BYTES_C2 = {
-    "preprocess_fwd": 217.00e6 + 40.97e6,
+    "preprocess_fwd": 232.95e6 + 42.25e6,
     "render_fwd": 65.70e6 + 18.59e6,
     "render_bwd": 117.31e6 + 6.87e6,
-    "preprocess_bwd": 285.00e6 + 242.47e6,
+    "preprocess_bwd": 285.00e6 + 242.51e6,
 }
 
 
@@ -149,8 +158,7 @@ def run_reference(args, rank, world):
     sc, dpix = make_scene(0, 1)
     line = {"impl": "reference", "metric": METRIC, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": {"workload": "C2: scene S, 1M Gaussians, SH degree 3, 1920x1080, 1 view, "
-                                                        "fwd+bwd", "P": P_GAUSS, "W": WIDTH, "H": HEIGHT}}
+            "data": "synthetic", "config": {"workload": WORKLOAD, "P": P_GAUSS, "W": WIDTH, "H": HEIGHT}}
     from checkers import REF_SO
     import torch
     if os.path.exists(REF_SO) and torch.cuda.is_available():
@@ -188,6 +196,124 @@ def run_reference(args, rank, world):
     return line
 
 
+def dp_check(step, t, dpix, rank, world, dev):
+    """N > 1, once before timing: the gradients every rank holds after one exchanged step against the sum of the N
+    views' gradients rendered by THIS rank alone, one view after the other (the batch sum of
+    train_stacked_transformer.py:203-222 on one device).  -> max over ranks of max|a - b| / max|b| per tensor."""
+    import torch
+    import torch.distributed as dist
+    import gsr_scenes as S
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    _, got = step(t)
+    got = [g.clone() for g in got]
+    rasters = []
+    for r in range(world):
+        cam = S.look_at_camera(WIDTH, HEIGHT, 60.0, -15.0 + 30.0 * r / (world - 1))
+        c = {k: torch.from_numpy(cam[k]).to(dev) for k in ("viewmatrix", "projmatrix", "campos")}
+        rasters.append(GaussianRasterizer(GaussianRasterizationSettings(
+            HEIGHT, WIDTH, cam["tanfovx"], cam["tanfovy"], t["bg"], 1.0, c["viewmatrix"], c["projmatrix"], SH_DEG,
+            c["campos"], False, False)))
+
+    def batch_sum():
+        want = None
+        for raster in rasters:
+            leaves = {k: t[k].detach().requires_grad_(True) for k in LEAVES}
+            color, _ = raster(means3D=leaves["means3D"], means2D=torch.zeros_like(leaves["means3D"]),
+                              opacities=leaves["opacities"], shs=leaves["sh"], scales=leaves["scales"],
+                              rotations=leaves["rotations"])
+            color.backward(dpix)
+            g = [leaves[k].grad for k in LEAVES]
+            want = g if want is None else [a + b for a, b in zip(want, g)]
+        return want
+    # The blend backward's fp32 atomics are order-nondeterministic: two single-rank sums of the same batch differ
+    # by up to ~1e-3 of max on the ill-conditioned tensors (scales, rotations) at this size.  The bar per tensor is
+    # therefore max(1e-3, 3 x that self-deviation), as in tests/test_gpu_parity.py.
+    want, again = batch_sum(), batch_sum()
+    rel = lambda a, b: (a - b).abs().max() / b.abs().max().clamp_min(1e-30)
+    errs = torch.stack([rel(a, b) for a, b in zip(got, want)])
+    self_dev = torch.stack([rel(a, b) for a, b in zip(again, want)])
+    dist.all_reduce(errs, op=dist.ReduceOp.MAX)
+    dist.all_reduce(self_dev, op=dist.ReduceOp.MAX)
+    return {"max_rel_err": {k: float(e) for k, e in zip(LEAVES, errs)},
+            "single_rank_self_deviation": {k: float(e) for k, e in zip(LEAVES, self_dev)},
+            "bar": {k: max(1e-3, 3.0 * float(e)) for k, e in zip(LEAVES, self_dev)}}
+
+
+def c3_record(rank, world, dev, steps=6, warmup=2, peer=True, multimem=True, gather="nccl"):
+    """BASELINE configs[2] ("C3") next to the C2 line: 3 M Gaussians, a batch of 8 views on a 30-degree arc at
+    1080p, STRONG scaling -- rank 0 alone renders all 8 views (t_1), then the batch is split over the N ranks with
+    the gsr_dp exchange (t_N); efficiency = t_1 / (N * t_N).  Device time, max over ranks."""
+    import torch
+    import torch.distributed as dist
+    import gsr_dp
+    import gsr_scenes as S
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    P, views = 3_000_000, 8
+    sc = S.scene_S(P, WIDTH, HEIGHT, seed=0)
+    t = {k: torch.from_numpy(np.ascontiguousarray(sc[k])).to(dev) for k in LEAVES + ("bg",)}
+    dpix = torch.from_numpy(S.upstream_grad(WIDTH, HEIGHT, 1)).to(dev)
+    rasters = []
+    for yaw in np.linspace(-15.0, 15.0, views):
+        cam = S.look_at_camera(WIDTH, HEIGHT, 60.0, float(yaw))
+        c = {k: torch.from_numpy(cam[k]).to(dev) for k in ("viewmatrix", "projmatrix", "campos")}
+        rasters.append(GaussianRasterizer(GaussianRasterizationSettings(
+            HEIGHT, WIDTH, cam["tanfovx"], cam["tanfovy"], t["bg"], 1.0, c["viewmatrix"], c["projmatrix"], SH_DEG,
+            c["campos"], False, False)))
+
+    def render_backward(v):
+        leaves = {k: t[k].detach().requires_grad_(True) for k in LEAVES}
+        color, _ = rasters[v](means3D=leaves["means3D"], means2D=torch.zeros_like(leaves["means3D"]),
+                              opacities=leaves["opacities"], shs=leaves["sh"], scales=leaves["scales"],
+                              rotations=leaves["rotations"])
+        color.backward(dpix)
+        return {k: leaves[k].grad for k in LEAVES}
+
+    def timed(r_, w_):
+        shapes = {k: tuple(t[k].shape) for k in gsr_dp.SMALL_LEAVES}
+        if peer and w_ > 1:
+            ex = gsr_dp.PeerExchange(views, P, shapes, dev, r_, w_, use_multimem=multimem, gather=gather)
+            flat = ex.flat
+        else:
+            flat = gsr_dp.FlatGrads(shapes, dev)
+            ex = gsr_dp.FactorExchange((views + w_ - 1) // w_, P, dev, w_)
+
+        def rb(v, _ex):
+            with gsr_dp.capture_sh_factors(ex), gsr_dp.grads_into(flat):
+                return render_backward(v)
+
+        def one():
+            if peer and w_ > 1:
+                return gsr_dp.dp_step_peer(rb, views, ex, t["means3D"], SH_DEG, M_COEF)
+            return gsr_dp.dp_step_factored(rb, views, flat, r_, w_, t["means3D"], SH_DEG, M_COEF, exchange=ex)
+        for _ in range(warmup):
+            g = one()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            g = one()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / steps, float(sum(g[k].double().abs().sum() for k in LEAVES))
+
+    dist.barrier()
+    t1 = torch.zeros(2, device=dev, dtype=torch.float64)
+    if rank == 0:  # the single-GPU reference time of the same batch (no collective: world = 1 inside gsr_dp)
+        ms1, sum1 = timed(0, 1)
+        t1 += torch.tensor([ms1, sum1], device=dev, dtype=torch.float64)
+    dist.barrier()
+    dist.broadcast(t1, 0)
+    msN, sumN = timed(rank, world)
+    tt = torch.tensor([msN], device=dev)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    msN = float(tt[0])
+    return {"workload": "C3: scene S, 3M Gaussians SH3, batch of 8 views on a 30-degree arc, 1920x1080, fwd+bwd, "
+                        "batch split over the ranks (strong scaling)",
+            "ms_per_batch": msN, "ms_per_batch_1gpu": float(t1[0]), "views_per_s": 8 * 1000.0 / msN,
+            "gaussians_per_s": P * 8 * 1000.0 / msN, "efficiency_vs_1": float(t1[0]) / (world * msN),
+            "grad_abs_sum": sumN, "grad_abs_sum_1gpu": float(t1[1]), "steps": steps}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -195,21 +321,32 @@ def run_ours(args, rank, world, local_rank):
     dev = torch.device("cuda", local_rank)
     torch.cuda.set_device(dev)
     sc, dpix_np = make_scene(rank, world)
-    host = {k: torch.from_numpy(np.ascontiguousarray(sc[k])).pin_memory() for k in TENSORS}
-    t = {k: v.to(dev) for k, v in host.items()}
-    dpix_host = torch.from_numpy(dpix_np).pin_memory()
-    dpix = dpix_host.to(dev)
+    t = {k: torch.from_numpy(np.ascontiguousarray(sc[k])).to(dev) for k in TENSORS}
+    # e2e leg: the Gaussians are replicated, so rank r keeps only ITS 1/N slice of every parameter array in pinned
+    # host memory; per step it copies that slice and the ranks all-gather the rest over NVLink (N = 1: the whole array)
+    rows = (P_GAUSS + world - 1) // world
+    lo = rank * rows
+    host = {k: torch.from_numpy(np.ascontiguousarray(sc[k][lo:lo + rows])).pin_memory() for k in LEAVES}
+    dpix = torch.from_numpy(dpix_np).to(dev)
     settings = GaussianRasterizationSettings(HEIGHT, WIDTH, sc["tanfovx"], sc["tanfovy"], t["bg"], 1.0,
                                              t["viewmatrix"], t["projmatrix"], SH_DEG, t["campos"], False, False)
     raster = GaussianRasterizer(settings)
     loss_host = torch.zeros(1).pin_memory()
     stats = {}
     flat = None
+    pg_param = None
     if world > 1:
         import gsr_dp
         keep = LEAVES if args.dp_exchange == "allreduce" else gsr_dp.SMALL_LEAVES
-        flat = gsr_dp.FlatGrads({k: tuple(t[k].shape) for k in keep}, dev)
+        peer = None
+        if args.dp_exchange == "peer":
+            peer = gsr_dp.PeerExchange(world, P_GAUSS, {k: tuple(t[k].shape) for k in keep}, dev, rank, world,
+                                       use_multimem=not args.no_multimem, gather=args.peer_gather)
+            flat = peer.flat
+        else:
+            flat = gsr_dp.FlatGrads({k: tuple(t[k].shape) for k in keep}, dev)
         exchange = gsr_dp.FactorExchange(1, P_GAUSS, dev, world) if args.dp_exchange == "factors" else None
+        pg_param = dist.new_group(backend="nccl")  # own communicator: parameter all-gathers of the e2e leg
 
     want = {"loss": False}
 
@@ -238,6 +375,12 @@ def run_ours(args, rank, world, local_rank):
                     box["loss"], g = render_backward(src)
                 return g
             g = gsr_dp.dp_step(rb, world, flat, rank, world)
+        elif args.dp_exchange == "peer":
+            def rb(_v, _ex):
+                with gsr_dp.capture_sh_factors(peer), gsr_dp.grads_into(flat):
+                    box["loss"], g = render_backward(src)
+                return g
+            g = gsr_dp.dp_step_peer(rb, world, peer, src["means3D"], SH_DEG, M_COEF)
         else:
             def rb(_v, _ex):
                 with gsr_dp.capture_sh_factors(exchange), gsr_dp.grads_into(flat):
@@ -255,6 +398,8 @@ def run_ours(args, rank, world, local_rank):
     for _ in range(max(args.warmup, 3)):
         step(t)
     sync_all()
+    check = dp_check(step, t, dpix, rank, world, dev) if world > 1 else None
+    sync_all()
     if args.timeline:
         from torch.profiler import ProfilerActivity, profile
         with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as tp:
@@ -269,24 +414,26 @@ def run_ours(args, rank, world, local_rank):
                     f.write("%9.1f %8.1f  %s\n" % (e.time_range.start - t0, e.time_range.end - e.time_range.start,
                                                     e.name[:90]))
         return None
-    # ---- timed region 1: inputs resident in HBM ("value"); per-stage device times recorded by the library
+    # ---- timed region 1: inputs resident in HBM ("value"); per-stage device times recorded by the library.  The
+    # clock sampler runs over BOTH timed regions (region 1 alone is shorter than a few nvidia-smi periods).
     clocks = ClockSampler(local_rank) if rank == 0 else None
     _lib.profile_enable(True)
+    _lib.launch_count(reset=True)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for _ in range(args.steps):
         step(t)
     b.record()
     sync_all()
+    launches = _lib.launch_count(reset=True)  # counted inside the library at every launch site
     ms = a.elapsed_time(b) / args.steps
     prof = _lib.profile_read()
     _lib.profile_enable(False)
-    clk = clocks.stop() if clocks else None
     # ---- timed region 2: end to end from pinned host buffers through the same public API.  Every step's inputs are
-    # copied host->device inside the timed region; the copy of step s+1 (copy stream, second buffer set) overlaps
-    # the compute of step s, and every step ends with a device->host read of its loss.
+    # copied host->device inside the timed region; the copy (+ all-gather) of step s+1 (copy stream, second buffer
+    # set) overlaps the compute of step s, and every step ends with a device->host read of its loss.
     copy_stream = torch.cuda.Stream(device=dev)
-    bufs = [{k: torch.empty_like(t[k]) for k in LEAVES} for _ in range(2)]
+    bufs = [{k: torch.empty((rows * world,) + tuple(t[k].shape[1:]), device=dev) for k in LEAVES} for _ in range(2)]
     ready = [torch.cuda.Event() for _ in range(2)]
     consumed = [torch.cuda.Event() for _ in range(2)]
 
@@ -295,7 +442,10 @@ def run_ours(args, rank, world, local_rank):
         with torch.cuda.stream(copy_stream):
             copy_stream.wait_event(consumed[b])  # the step that last used this buffer set has finished
             for k in LEAVES:
-                bufs[b][k].copy_(host[k], non_blocking=True)
+                bufs[b][k][lo:lo + host[k].shape[0]].copy_(host[k], non_blocking=True)
+            if world > 1:
+                for k in LEAVES:
+                    dist.all_gather_into_tensor(bufs[b][k], bufs[b][k][lo:lo + rows], group=pg_param)
             ready[b].record(copy_stream)
 
     def e2e_run(n_):
@@ -309,7 +459,7 @@ def run_ours(args, rank, world, local_rank):
             b = s_ & 1
             cur.wait_event(ready[b])
             want["loss"] = True
-            loss, _ = step(bufs[b])
+            loss, _ = step({k: bufs[b][k][:P_GAUSS] for k in LEAVES})
             consumed[b].record(cur)
             loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
             cur.synchronize()
@@ -321,11 +471,16 @@ def run_ours(args, rank, world, local_rank):
     e2e_run(n_e2e)
     b2.record()
     sync_all()
+    want["loss"] = False
+    clk = clocks.stop() if clocks else None
     ms_e2e = a2.elapsed_time(b2) / n_e2e
     if world > 1:
         tt = torch.tensor([ms, ms_e2e], device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms, ms_e2e = float(tt[0]), float(tt[1])
+    c3 = c3_record(rank, world, dev, peer=args.dp_exchange == "peer", multimem=not args.no_multimem,
+                   gather=args.peer_gather) \
+        if (world > 1 and not args.no_c3) else None
     if rank != 0:
         return None
     # ---- bookkeeping for the JSON line
@@ -340,35 +495,59 @@ def run_ours(args, rank, world, local_rank):
     dom = max(a_stage, key=lambda s: per_stage_ms.get(s, 0.0))
     dom_ms = per_stage_ms[dom]
     achieved = a_stage[dom] / (dom_ms * 1e-3) / 1e9
-    kernels_per_step = 1 + 12 + 3 + 1 + 1 + 1 + 1
     h2d = sum(host[k].numel() * 4 for k in LEAVES)
+    same_view = (V == NCU_CAPTURE["V"] and R == NCU_CAPTURE["R"])
     value = world * 1000.0 / ms
+    # the HBM-bound kernels against the same roof (the dominant kernel is an issue-bound blend kernel)
+    hbm_kernels = {s: {"algorithmic_bytes": a_stage[s], "kernel_ms": per_stage_ms[s],
+                       "achieved": a_stage[s] / (per_stage_ms[s] * 1e-3) / 1e9,
+                       "frac": a_stage[s] / (per_stage_ms[s] * 1e-3) / 1e9 / peak}
+                   for s in ("preprocess_fwd", "preprocess_bwd") if per_stage_ms.get(s)}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "gaussians_per_s": value * P_GAUSS,
-        "config": {"workload": "C2: scene S (seed 0), 1M Gaussians, SH degree 3, 1920x1080, 1 view per GPU, fwd+bwd"
-                               + ("" if world == 1 else ", NCCL all-reduce of 236 B/Gaussian gradients"
-                                  if args.dp_exchange == "allreduce" else
-                                  ", NCCL all-reduce of 44 B/Gaussian + all-gather of 12 B/Gaussian/view SH factors, "
-                                  "SH gradient rebuilt locally"),
+        "config": {"workload": WORKLOAD,
+                   "exchange": "none" if world == 1 else "NCCL all-reduce of 236 B/Gaussian gradients"
+                   if args.dp_exchange == "allreduce" else
+                   "NCCL all-reduce of 44 B/Gaussian + all-gather of 12 B/Gaussian/view SH factors, SH gradient "
+                   "rebuilt locally" if args.dp_exchange == "factors" else
+                   "SH factor records (12 B/Gaussian/view) gathered by %s and summed by our rebuild kernel; all-reduce "
+                   "of 44 B/Gaussian by our %s kernel over the symmetric allocation"
+                   % ({"nccl": "one NCCL all-gather", "copy": "peer-to-peer copies", "fused": "remote reads inside "
+                       "the rebuild kernel"}[args.peer_gather],
+                      "NVSwitch multimem" if (peer is not None and peer.flat_mc) else "two-shot P2P"),
                    "P": P_GAUSS, "visible": V, "num_rendered": R, "W": WIDTH, "H": HEIGHT,
                    "l2": "inputs (236 MB) + scratch exceed the 126 MB L2; no explicit flush"},
         "clocks": clk,
-        "e2e": {"value": world * 1000.0 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-                "ms_per_step": ms_e2e},
-        "gpu_launches": kernels_per_step * args.steps,
+        "e2e": {"value": world * 1000.0 / ms_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                "h2d_bytes_per_step_all_ranks": h2d * world, "d2h_bytes_per_step": 4, "ms_per_step": ms_e2e,
+                "inputs": "each rank copies its 1/N slice of the replicated parameters from pinned host memory; "
+                          "NCCL all-gather over NVLink fills in the rest" if world > 1 else
+                          "all parameters copied from pinned host memory every step"},
+        "gpu_launches": launches,
+        "gpu_launches_per_step": launches / args.steps,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "peak_kind": peak_kind,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": NCU_DRAM_BYTES_C2.get(dom),
-                     "traffic_source": "profiles/r01_ncu_full_metrics.txt (ncu --set full, same workload)",
+                     "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": NCU_DRAM_BYTES_C2.get(dom) if same_view else None,
+                     "traffic_source": NCU_CAPTURE["source"] + " (ncu --set full, same view)" if same_view else None,
                      "algorithmic_bytes": a_stage[dom], "kernel_ms": dom_ms,
                      "note": "alpha blending is FP32/MUFU-pipe bound, not HBM bound; the HBM fraction is reported "
-                             "because BASELINE.json's metric asks for it"},
+                             "because BASELINE.json's metric asks for it; roofline_hbm_kernels lists the two "
+                             "HBM-bound kernels against the same roof"},
+        "roofline_hbm_kernels": hbm_kernels,
         "roofline_step": {"algorithmic_bytes": a_total, "achieved": a_total / (ms * 1e-3) / 1e9, "peak": peak,
                           "unit": "GB/s", "frac": a_total / (ms * 1e-3) / 1e9 / peak,
                           "frac_of_nominal_8000": a_total / (ms * 1e-3) / 1e9 / 8000.0},
         "stage_ms": per_stage_ms,
     }
+    if check is not None:
+        check["ok"] = all(check["max_rel_err"][k] <= check["bar"][k] for k in LEAVES)
+        check["against"] = "sum of the N views' gradients rendered on one rank (bar: max(1e-3, 3 x the deviation " \
+                           "between two such single-rank sums))"
+        line["dp_check"] = check
+    if c3 is not None:
+        line["c3"] = c3
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(sc, dpix_np)
     return line

@@ -27,6 +27,7 @@
 #include "render_bwd.cuh"
 #include "render_fwd.cuh"
 #include "sh_exchange.cuh"
+#include "peer_exchange.cuh"
 
 using namespace gsr;
 
@@ -641,6 +642,58 @@ int gsr_sh_grad_from_factors(int32_t P, int32_t D, int32_t M, int32_t V, const f
     sh_grad_from_factors_kernel<false><<<blocks, PB_THREADS, 0, stream>>>(P, D, M, V, means3D, campos, factors,
                                                                          dL_dsh, accumulate), GSR_LAUNCHED(1);
   GSR_STAGE("sh_grad_from_factors", 0, stream);
+  return GSR_OK;
+}
+
+// ---- data-parallel exchange over NVLink peer memory (gsr_dp.PeerExchange)
+int gsr_peer_allreduce(int32_t world, int32_t rank, const uint64_t* peer_ptrs, uint64_t multicast_ptr, int64_t n_floats,
+                       void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (world < 1 || world > PEER_MAX_RANKS || rank < 0 || rank >= world || n_floats < 0 || (n_floats & 3))
+    return fail(GSR_ERR_INVALID, "gsr_peer_allreduce: bad world / rank / n_floats (a multiple of 4)");
+  if (n_floats == 0 || world == 1) return GSR_OK;
+  if (!peer_ptrs) return fail(GSR_ERR_INVALID, "gsr_peer_allreduce: NULL peer_ptrs");
+  const size_t total4 = (size_t)n_floats / 4, n4 = (total4 + world - 1) / world;
+  const int blocks = (int)std::min<size_t>((n4 + 255) / 256, (size_t)148 * 8);
+  if (multicast_ptr) {
+    const int mblocks = (int)std::min<size_t>((n4 + 1023) / 1024, (size_t)148 * 8);
+    peer_allreduce_multimem_kernel<<<mblocks, 256, 0, stream>>>((float4*)multicast_ptr, rank, n4, total4), GSR_LAUNCHED(1);
+  } else {
+    PeerBufs b;
+    memset(&b, 0, sizeof(b));
+    for (int p = 0; p < world; p++) {
+      if (!peer_ptrs[p] || (peer_ptrs[p] & 15u)) return fail(GSR_ERR_INVALID, "gsr_peer_allreduce: bad peer pointer");
+      b.p[p] = (float4*)peer_ptrs[p];
+    }
+    switch (world) {
+      case 2: peer_allreduce_kernel<2><<<blocks, 256, 0, stream>>>(b, rank, n4, total4), GSR_LAUNCHED(1); break;
+      case 4: peer_allreduce_kernel<4><<<blocks, 256, 0, stream>>>(b, rank, n4, total4), GSR_LAUNCHED(1); break;
+      case 8: peer_allreduce_kernel<8><<<blocks, 256, 0, stream>>>(b, rank, n4, total4), GSR_LAUNCHED(1); break;
+      default: return fail(GSR_ERR_INVALID, "gsr_peer_allreduce: world must be 2, 4 or 8 without a multicast mapping");
+    }
+  }
+  GSR_STAGE("peer_allreduce", 0, stream);
+  return GSR_OK;
+}
+
+int gsr_sh_grad_from_peers(int32_t P, int32_t D, int32_t M, int32_t V, const float* means3D,
+                           const uint64_t* view_ptrs, float* dL_dsh, int32_t accumulate, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0 || V < 0 || V > PEER_MAX_VIEWS || M != 16 || D < 0 || D > 3)
+    return fail(GSR_ERR_INVALID, "gsr_sh_grad_from_peers: bad P / V (<= 64) / D, or M != 16");
+  if (P == 0) return GSR_OK;
+  if (!means3D || !dL_dsh || (V > 0 && !view_ptrs)) return fail(GSR_ERR_INVALID, "gsr_sh_grad_from_peers: NULL pointer");
+  if (!aligned16(dL_dsh)) return fail(GSR_ERR_INVALID, "gsr_sh_grad_from_peers: dL_dsh must be 16-byte aligned");
+  PeerViews pv;
+  memset(&pv, 0, sizeof(pv));
+  for (int v = 0; v < V; v++) {
+    if (!view_ptrs[v]) return fail(GSR_ERR_INVALID, "gsr_sh_grad_from_peers: NULL view pointer");
+    pv.fac[v] = (const float*)view_ptrs[v];
+  }
+  const int blocks = (P + PB_THREADS - 1) / PB_THREADS;
+  sh_grad_from_peers_kernel<8><<<blocks, PB_THREADS, PB_THREADS * 13 * 16, stream>>>(P, D, V, pv, means3D, dL_dsh,
+                                                                                       accumulate), GSR_LAUNCHED(1);
+  GSR_STAGE("sh_grad_from_peers", 0, stream);
   return GSR_OK;
 }
 

@@ -31,7 +31,19 @@ def shard_views(n_views: int, rank: int, world: int) -> List[int]:
 class FlatGrads:
     """One contiguous fp32 buffer with a view per parameter, in LEAVES order."""
 
-    def __init__(self, shapes: Dict[str, Sequence[int]], device, bucket_bytes: int = 0):
+    @staticmethod
+    def numel(shapes: Dict[str, Sequence[int]]) -> int:
+        n = 0
+        for k in LEAVES:
+            if k in shapes:
+                m = 1
+                for d in shapes[k]:
+                    m *= int(d)
+                n += (m + 3) & ~3
+        return n
+
+    def __init__(self, shapes: Dict[str, Sequence[int]], device, bucket_bytes: int = 0, flat: torch.Tensor = None):
+        """flat: caller-provided storage of FlatGrads.numel(shapes) floats (e.g. a symmetric-memory allocation)."""
         self.shapes = {k: tuple(shapes[k]) for k in LEAVES if k in shapes}
         n = 0
         self.slices = {}
@@ -41,7 +53,11 @@ class FlatGrads:
                 m *= int(d)
             self.slices[k] = (n, n + m)
             n += (m + 3) & ~3  # every view starts 16-byte aligned (the kernels' 128-bit stores); padding stays 0
-        self.flat = torch.zeros(n, dtype=torch.float32, device=device)
+        if flat is not None:
+            if flat.numel() != n or flat.dtype != torch.float32 or not flat.is_contiguous():
+                raise ValueError("flat must be a contiguous float32 tensor of %d elements" % n)
+            flat.zero_()
+        self.flat = flat if flat is not None else torch.zeros(n, dtype=torch.float32, device=device)
         self.views = {k: self.flat[a:b].view(self.shapes[k]) for k, (a, b) in self.slices.items()}
         self.bucket_elems = bucket_bytes // 4 if bucket_bytes else 0
         self._first = True
@@ -60,12 +76,13 @@ class FlatGrads:
                 v.add_(g)
         self._first = False
 
-    def all_reduce(self, group=None, async_op: bool = False):
-        """SUM over ranks.  bucket_bytes > 0 splits the buffer so that early buckets start while later ones queue."""
+    def all_reduce(self, group=None, async_op: bool = False, world=None):
+        """SUM over ranks.  bucket_bytes > 0 splits the buffer so that early buckets start while later ones queue.
+        world = 1: no collective even inside an initialised process group (a single-rank reference run)."""
         if self._first:
             self.flat.zero_()  # this rank rendered no view this step
             self._first = False
-        if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        if world == 1 or not dist.is_initialized() or dist.get_world_size(group) == 1:
             return []
         if not self.bucket_elems or self.bucket_elems >= self.flat.numel():
             w = dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
@@ -86,7 +103,7 @@ def dp_step(render_backward: Callable[[int], Dict[str, torch.Tensor]], n_views: 
     flat.zero_()
     for v in shard_views(n_views, rank, world):
         flat.add_(render_backward(v))
-    for w in flat.all_reduce(group=group, async_op=True):
+    for w in flat.all_reduce(group=group, async_op=True, world=world):
         w.wait()
     return flat.views
 
@@ -245,10 +262,178 @@ def dp_step_factored(render_backward: Callable[..., Dict[str, torch.Tensor]], n_
         if ex.n != seen + 1:
             raise RuntimeError("render_backward must hand exactly one view's SH factors to the exchange")
     ex.pad()  # same collective order on every rank: all slots first, then the all-reduce
-    works = flat_small.all_reduce(group=group, async_op=True)
+    works = flat_small.all_reduce(group=group, async_op=True, world=world)
     cam_all, fac_all = ex.finish()
     out = dict(flat_small.views)
     out["sh"] = rebuild(means3D, cam_all, fac_all, degree, M)
     for w in works:
         w.wait()
+    return out
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# The same exchange with OUR kernels over NVLink peer memory instead of NCCL calls (csrc/peer_exchange.cuh).  The
+# batch's SH factors and the small gradients live in ONE symmetric allocation per rank (torch's symmetric memory:
+# plumbing -- allocation, peer mapping and the device-side barrier); after the local views,
+#   barrier -> [ gsr_sh_grad_from_peers on a side stream  ||  gsr_peer_allreduce ] -> barrier.
+# The gather of the factors never materialises (the rebuild kernel reads each view's factors from the rank that
+# rendered it), and the all-reduce is one two-shot kernel (or NVSwitch multimem where the allocation has a multicast
+# mapping).  CUDA only; the gloo tests cover the NCCL-shaped path above, bench.py's dp_check covers this one on GPUs.
+class PeerExchange:
+    """Factor sink (buffer / emit protocol of diff_gaussian_rasterization) + FlatGrads over a symmetric allocation."""
+
+    def __init__(self, n_views: int, P: int, shapes_small: Dict[str, Sequence[int]], device, rank: int, world: int,
+                 group=None, use_multimem: bool = True, gather: str = "nccl"):
+        """gather: how the peers' view records reach this rank -- "nccl" (one all-gather launched when this rank's
+        last view has emitted its factors; fastest at 8 GPUs), "copy" (peer-to-peer copies by the copy engines) or
+        "fused" (the rebuild kernel reads the peers' records in place over NVLink)."""
+        import ctypes
+        import torch.distributed._symmetric_memory as symm
+        self.n_views, self.P, self.rank, self.world = n_views, P, rank, world
+        self.per_rank = (n_views + world - 1) // world
+        self.counts = [len(shard_views(n_views, r, world)) for r in range(world)]
+        self.slot = (3 * P + 4 + 3) & ~3  # floats per view record: P*3 factors, 3 camera floats, padding
+        n_flat = FlatGrads.numel(shapes_small)
+        self.buf = symm.empty(self.per_rank * self.slot + n_flat, dtype=torch.float32, device=device)
+        self.hdl = symm.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        self.flat_off = self.per_rank * self.slot
+        self.flat = FlatGrads(shapes_small, device, flat=self.buf[self.flat_off:])
+        self.n_flat = n_flat
+        ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.flat_ptrs = (ctypes.c_uint64 * world)(*[p + 4 * self.flat_off for p in ptrs])
+        mc = int(self.hdl.multicast_ptr) if (use_multimem and getattr(self.hdl, "has_multicast_support", False)) else 0
+        self.flat_mc = mc + 4 * self.flat_off if mc else 0
+        # The batch's view records as the rebuild kernel sees them: this rank's own records in place, the peers'
+        # records in a local staging copy that the copy engines fill over NVLink (no SM is spent on the gather, and
+        # it runs under preprocess_bwd, which is HBM bound; the rebuild -- HBM bound too -- then runs under the
+        # all-reduce, which is link bound).
+        if gather not in ("nccl", "copy", "fused"):
+            raise ValueError("gather must be 'nccl', 'copy' or 'fused'")
+        self.gather, self.group = gather, group
+        pairs = [(j, r) for j in range(self.per_rank) for r in range(world) if j < self.counts[r]]
+        remote = [(j, r) for (j, r) in pairs if r != rank]
+        self.remote, self.gathered = [], None
+        if gather == "copy":
+            self.stage = torch.empty(max(len(remote), 1) * self.slot, dtype=torch.float32, device=device)
+            self.remote = [(self.stage[k * self.slot:(k + 1) * self.slot],
+                            self.hdl.get_buffer(r, (self.slot,), torch.float32, j * self.slot))
+                           for k, (j, r) in enumerate(remote)]
+            where = {jr: self.stage.data_ptr() + 4 * k * self.slot for k, jr in enumerate(remote)}
+        elif gather == "nccl":
+            self.gathered = torch.empty(world, self.per_rank * self.slot, dtype=torch.float32, device=device)
+            where = {(j, r): self.gathered.data_ptr() + 4 * (r * self.per_rank + j) * self.slot for (j, r) in remote}
+        else:
+            where = {(j, r): ptrs[r] + 4 * j * self.slot for (j, r) in remote}
+        views = [where.get((j, r), ptrs[rank] + 4 * j * self.slot) for (j, r) in pairs]
+        self.view_ptrs = (ctypes.c_uint64 * max(len(views), 1))(*views)
+        self.V = len(views)
+        self.copy_streams = [torch.cuda.Stream(device=device, priority=-1) for _ in range(2)]
+        self.side = torch.cuda.Stream(device=device, priority=-1)  # must get SMs while preprocess_bwd is dispatched
+        self.n = 0
+        self._sh = None
+        self._early = None
+
+    def begin(self, means3D: torch.Tensor = None, degree: int = 0, M: int = 16, out_sh: torch.Tensor = None):
+        """Start of a step.  With means3D given, the SH rebuild is launched (side stream) the moment this rank's last
+        view has emitted its factors -- i.e. between the two stages of that view's backward, so that the remote
+        reads run under preprocess_bwd -- instead of inside exchange()."""
+        self.n = 0
+        self._sh = None
+        self._early = None
+        if means3D is not None:
+            if M != 16:
+                raise ValueError("PeerExchange is built for M = 16")
+            self._early = (means3D, int(degree), int(M), out_sh)
+        if self.counts[self.rank] == 0 and self._early is not None:
+            self._launch_rebuild(*self._early)
+
+    def _launch_rebuild(self, means3D, degree, M, out_sh):
+        from diff_gaussian_rasterization import _lib
+        dev = means3D.device
+        sh = out_sh if out_sh is not None else torch.empty(self.P, M, 3, dtype=torch.float32, device=dev)
+        cur = torch.cuda.current_stream(dev)
+        if self.gather == "nccl":
+            # one all-gather of the ranks' record blocks, launched here (between the two stages of the last view's
+            # backward): it runs under preprocess_bwd on NCCL's stream
+            work = dist.all_gather_into_tensor(self.gathered.view(-1), self.buf[:self.per_rank * self.slot],
+                                               group=self.group, async_op=True)
+            with torch.cuda.stream(self.side):
+                work.wait()
+                _lib.check(_lib.lib.gsr_sh_grad_from_peers(self.P, degree, M, self.V, means3D.data_ptr(),
+                                                           self.view_ptrs, sh.data_ptr(), 0, self.side.cuda_stream))
+        else:
+            self.side.wait_stream(cur)
+            with torch.cuda.stream(self.side):
+                self.hdl.barrier(channel=0)  # every rank's factors of this step are complete
+            for cs in self.copy_streams:
+                cs.wait_stream(self.side)
+            for k, (dst, src) in enumerate(self.remote):  # peer -> local over NVLink, copy engines, two streams
+                with torch.cuda.stream(self.copy_streams[k & 1]):
+                    dst.copy_(src, non_blocking=True)
+            with torch.cuda.stream(self.side):
+                for cs in self.copy_streams:
+                    self.side.wait_stream(cs)
+                _lib.check(_lib.lib.gsr_sh_grad_from_peers(self.P, degree, M, self.V, means3D.data_ptr(),
+                                                           self.view_ptrs, sh.data_ptr(), 0, self.side.cuda_stream))
+        sh.record_stream(self.side)
+        self._sh = sh
+
+    # -- the sink protocol of diff_gaussian_rasterization
+    def buffer(self, P, device):
+        if self.n >= self.per_rank:
+            raise ValueError("more local views than per_rank")
+        if P != self.P:
+            raise ValueError("PeerExchange was sized for %d Gaussians, got %d" % (self.P, P))
+        j = self.n
+        return self.buf[j * self.slot:j * self.slot + 3 * P].view(P, 3)
+
+    def emit(self, campos, factors):
+        j = self.n
+        if j >= self.per_rank:
+            raise ValueError("more local views than per_rank")
+        rec = self.buf[j * self.slot:(j + 1) * self.slot]
+        if factors.data_ptr() != rec.data_ptr():
+            rec[:3 * self.P].copy_(factors.reshape(-1))
+        rec[3 * self.P:3 * self.P + 3].copy_(campos.reshape(3))
+        self.n = j + 1
+        if self.n == self.counts[self.rank] and self._early is not None:
+            self._launch_rebuild(*self._early)
+
+    def exchange(self, means3D: torch.Tensor, degree: int, M: int, out_sh: torch.Tensor = None):
+        """After this rank's views: all-reduce of the small gradients (in place in self.flat) and the batch's summed
+        dL/dsh (P,M,3), rebuilt from every rank's factors.  Returns the SH gradient."""
+        from diff_gaussian_rasterization import _lib
+        if M != 16:
+            raise ValueError("PeerExchange is built for M = 16")
+        if self.n != self.counts[self.rank]:
+            raise RuntimeError("this rank rendered %d views, its share of the batch is %d" % (self.n, self.counts[self.rank]))
+        if self.flat._first:
+            self.flat.flat.zero_()
+            self.flat._first = False
+        dev = means3D.device
+        cur = torch.cuda.current_stream(dev)
+        if self._sh is None:  # not launched early: factors barrier + rebuild now
+            self._launch_rebuild(means3D, int(degree), int(M), out_sh)
+        self.hdl.barrier(channel=1)  # every rank's small gradients are complete
+        _lib.check(_lib.lib.gsr_peer_allreduce(self.world, self.rank, self.flat_ptrs, self.flat_mc, self.n_flat,
+                                               cur.cuda_stream))
+        cur.wait_stream(self.side)
+        self.hdl.barrier(channel=2)  # all sums delivered; every peer is done reading this rank's factors
+        sh, self._sh = self._sh, None
+        return sh
+
+
+def dp_step_peer(render_backward: Callable[..., Dict[str, torch.Tensor]], n_views: int, ex: "PeerExchange",
+                 means3D: torch.Tensor, degree: int, M: int) -> Dict[str, torch.Tensor]:
+    """dp_step_factored over peer memory: `render_backward(v, ex)` runs one view's forward + backward inside
+    `capture_sh_factors(ex)` (and `grads_into(ex.flat)`), returning the SMALL_LEAVES gradients."""
+    ex.begin(means3D, degree, M)
+    ex.flat.zero_()
+    for v in shard_views(n_views, ex.rank, ex.world):
+        seen = ex.n
+        ex.flat.add_(render_backward(v, ex))
+        if ex.n != seen + 1:
+            raise RuntimeError("render_backward must hand exactly one view's SH factors to the exchange")
+    out = dict(ex.flat.views)
+    out["sh"] = ex.exchange(means3D, degree, M)
     return out

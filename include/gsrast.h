@@ -258,6 +258,21 @@ typedef struct gsr_adam_group {
 GSR_API int gsr_adam_step(int32_t n_groups, const gsr_adam_group* groups, double beta1, double beta2, double eps,
                           void* stream);
 
+/* Data-parallel exchange over NVLink peer memory (gsr_dp.PeerExchange; no reference counterpart -- the reference
+ * is single-GPU, the semantic is the batch sum of train_stacked_transformer.py:203-222 across ranks).
+ * gsr_peer_allreduce: in-place SUM over `world` ranks of n_floats floats (a multiple of 4).  peer_ptrs[p] = address, in
+ * THIS process, of rank p's buffer (a symmetric allocation; peer_ptrs[rank] is the local one); multicast_ptr != 0: the
+ * allocation's multicast address, the NVSwitch then reduces (multimem.ld_reduce / multimem.st).  The caller orders
+ * the ranks: every rank's buffer complete before any rank calls this, and nobody reads the result before every rank's
+ * call has finished (a device-side barrier on either side).
+ * gsr_sh_grad_from_peers: dL_dsh (P,16,3) (+)= sum over V views of basis(normalize(means3D - campos_v)) (x) f_v, with
+ * view_ptrs[v] = address of view v's record on the rank that rendered it: P*3 factor floats (gsr_backward_sh_factors)
+ * followed by the view's 3 camera-position floats. */
+GSR_API int gsr_peer_allreduce(int32_t world, int32_t rank, const uint64_t* peer_ptrs, uint64_t multicast_ptr,
+                               int64_t n_floats, void* stream);
+GSR_API int gsr_sh_grad_from_peers(int32_t P, int32_t D, int32_t M, int32_t V, const float* means3D,
+                                   const uint64_t* view_ptrs, float* dL_dsh, int32_t accumulate, void* stream);
+
 /* The depth sort of the forward on its own: stable ascending sort of n (uint32 key, uint32 value) pairs over all 32
  * key bits; the values of the result are the ORIGINAL INDICES of the keys (vals on entry is ignored), i.e. the
  * "value = Gaussian id" use of cub::DeviceRadixSort::SortPairs in DGR/cuda_rasterizer/rasterizer_impl.cu:300-308
