@@ -47,8 +47,13 @@ def parse():
                          "full 236 B/Gaussian")
     ap.add_argument("--peer-gather", default="nccl", choices=("nccl", "copy", "fused"),
                     help="peer exchange: how the SH-factor records travel (gsr_dp.PeerExchange)")
-    ap.add_argument("--no-multimem", action="store_true", help="peer exchange: two-shot P2P kernel even where the "
-                                                                "allocation has an NVSwitch multicast mapping")
+    ap.add_argument("--multimem", action="store_true",
+                    help="peer exchange: all-reduce through the allocation's NVSwitch multicast mapping "
+                         "(multimem.ld_reduce / multimem.st) instead of the two-shot P2P kernel (measured at 8 GPUs: "
+                         "2.12 vs 2.10 ms/step, profiles/r02_multigpu_exchange_experiments.txt)")
+    ap.add_argument("--c3-exchange", default="factors", choices=("factors", "peer"),
+                    help="exchange of the C3 record (measured at 8 GPUs: 3.11 ms/batch with the NCCL factor "
+                         "exchange, 3.20 with the peer exchange)")
     return ap.parse_args()
 
 
@@ -311,7 +316,9 @@ def c3_record(rank, world, dev, steps=6, warmup=2, peer=True, multimem=True, gat
                         "batch split over the ranks (strong scaling)",
             "ms_per_batch": msN, "ms_per_batch_1gpu": float(t1[0]), "views_per_s": 8 * 1000.0 / msN,
             "gaussians_per_s": P * 8 * 1000.0 / msN, "efficiency_vs_1": float(t1[0]) / (world * msN),
-            "grad_abs_sum": sumN, "grad_abs_sum_1gpu": float(t1[1]), "steps": steps}
+            "grad_abs_sum": sumN, "grad_abs_sum_1gpu": float(t1[1]), "steps": steps,
+            "exchange": "gsr_dp.PeerExchange" if peer else "gsr_dp.FactorExchange (NCCL all-gather of SH factors per "
+                                                           "view slot + all-reduce of 44 B/Gaussian)"}
 
 
 def run_ours(args, rank, world, local_rank):
@@ -341,7 +348,7 @@ def run_ours(args, rank, world, local_rank):
         peer = None
         if args.dp_exchange == "peer":
             peer = gsr_dp.PeerExchange(world, P_GAUSS, {k: tuple(t[k].shape) for k in keep}, dev, rank, world,
-                                       use_multimem=not args.no_multimem, gather=args.peer_gather)
+                                       use_multimem=args.multimem, gather=args.peer_gather)
             flat = peer.flat
         else:
             flat = gsr_dp.FlatGrads({k: tuple(t[k].shape) for k in keep}, dev)
@@ -478,7 +485,7 @@ def run_ours(args, rank, world, local_rank):
         tt = torch.tensor([ms, ms_e2e], device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         ms, ms_e2e = float(tt[0]), float(tt[1])
-    c3 = c3_record(rank, world, dev, peer=args.dp_exchange == "peer", multimem=not args.no_multimem,
+    c3 = c3_record(rank, world, dev, peer=args.c3_exchange == "peer", multimem=args.multimem,
                    gather=args.peer_gather) \
         if (world > 1 and not args.no_c3) else None
     if rank != 0:

@@ -28,6 +28,7 @@
 #include "render_fwd.cuh"
 #include "sh_exchange.cuh"
 #include "peer_exchange.cuh"
+#include "compact.cuh"
 
 using namespace gsr;
 
@@ -642,6 +643,61 @@ int gsr_sh_grad_from_factors(int32_t P, int32_t D, int32_t M, int32_t V, const f
     sh_grad_from_factors_kernel<false><<<blocks, PB_THREADS, 0, stream>>>(P, D, M, V, means3D, campos, factors,
                                                                          dL_dsh, accumulate), GSR_LAUNCHED(1);
   GSR_STAGE("sh_grad_from_factors", 0, stream);
+  return GSR_OK;
+}
+
+// ---- row compaction for densify / clone / split / prune
+int gsr_compact_scratch_bytes(int32_t P, size_t* bytes) {
+  if (P < 0 || !bytes) return fail(GSR_ERR_INVALID, "gsr_compact_scratch_bytes: bad arguments");
+  *bytes = align_up(4 * ((size_t)P / CP_BLOCK + 2)) + ALIGN;
+  return GSR_OK;
+}
+
+int gsr_compact_indices(int32_t P, const uint8_t* mask, int32_t* idx_out, int32_t add, int64_t* count_out,
+                        void* scratch, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0 || !count_out) return fail(GSR_ERR_INVALID, "gsr_compact_indices: bad arguments");
+  if (P == 0) {
+    GSR_CUDA(cudaMemsetAsync(count_out, 0, 8, stream), "compact count memset");
+    return GSR_OK;
+  }
+  if (!mask || !idx_out || !scratch) return fail(GSR_ERR_INVALID, "gsr_compact_indices: NULL pointer");
+  const int nb = (P + CP_BLOCK - 1) / CP_BLOCK;
+  uint32_t* counts = (uint32_t*)scratch;
+  compact_count_kernel<<<nb, CP_THREADS, 0, stream>>>(P, mask, counts), GSR_LAUNCHED(1);
+  compact_offsets_kernel<<<1, 1024, 0, stream>>>(nb, counts, (unsigned long long*)count_out), GSR_LAUNCHED(1);
+  compact_write_kernel<<<nb, CP_THREADS, 0, stream>>>(P, mask, counts, idx_out, add), GSR_LAUNCHED(1);
+  GSR_STAGE("compact_indices", 0, stream);
+  return GSR_OK;
+}
+
+int gsr_gather_rows(int32_t n_tables, const gsr_gather_table* tables, int64_t n_rows, const int32_t* idx,
+                    void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (n_tables < 0 || n_rows < 0) return fail(GSR_ERR_INVALID, "gsr_gather_rows: bad arguments");
+  if (n_tables == 0 || n_rows == 0) return GSR_OK;
+  if (!tables) return fail(GSR_ERR_INVALID, "gsr_gather_rows: NULL pointer");
+  for (int a0 = 0; a0 < n_tables; a0 += GATHER_MAX_TABLES) {
+    GatherArgs a;
+    memset(&a, 0, sizeof(a));
+    long long blocks = 0;
+    int k = 0;
+    for (int i = a0; i < n_tables && i < a0 + GATHER_MAX_TABLES; i++) {
+      const gsr_gather_table& s = tables[i];
+      if (s.row_floats < 0) return fail(GSR_ERR_INVALID, "gsr_gather_rows: row_floats < 0");
+      if (s.row_floats == 0) continue;
+      if (!s.src || !s.dst) return fail(GSR_ERR_INVALID, "gsr_gather_rows: NULL table pointer");
+      if (!s.idx && !idx) return fail(GSR_ERR_INVALID, "gsr_gather_rows: table without an index list");
+      a.t[k].src = s.src; a.t[k].dst = s.dst; a.t[k].idx = s.idx; a.t[k].row_floats = s.row_floats; a.t[k].first_block = (int)blocks;
+      blocks += (n_rows * s.row_floats + GATHER_ELEMS - 1) / GATHER_ELEMS;
+      if (blocks > 0x7fffffffLL) return fail(GSR_ERR_INVALID, "gsr_gather_rows: too many elements for one launch");
+      k++;
+    }
+    a.n_tables = k;
+    if (k == 0) continue;
+    gather_rows_kernel<<<(unsigned)blocks, GATHER_THREADS, 0, stream>>>(a, n_rows, idx), GSR_LAUNCHED(1);
+  }
+  GSR_STAGE("gather_rows", 0, stream);
   return GSR_OK;
 }
 

@@ -258,6 +258,26 @@ typedef struct gsr_adam_group {
 GSR_API int gsr_adam_step(int32_t n_groups, const gsr_adam_group* groups, double beta1, double beta2, double eps,
                           void* stream);
 
+/* Row compaction behind densify / clone / split / prune.  Replaces the boolean-mask indexing and
+ * torch.cat of scene/gaussian_model.py:273-327 (_prune_optimizer, prune_points, cat_tensors_to_optimizer): one
+ * index list per mask, then ONE launch that moves the rows of every parameter, Adam moment and statistics tensor.
+ * gsr_compact_indices: idx_out[k] = add + (index of the k-th non-zero mask byte), ascending = the order of
+ * tensor[mask]; the number of indices goes to count_out (device or pinned host int64).
+ * gsr_gather_rows: for every table, dst[j, :] = src[idx[j], :] for j < n_rows; idx[j] < 0 writes a row of zeros
+ * (fresh Adam moments); a table may bring its own index list (parameters and their moments differ in the new rows).  Bit-identical to the torch statements (pure data movement). */
+typedef struct gsr_gather_table {
+  const float* src;
+  float* dst;
+  const int32_t* idx; /* NULL: the call's shared index list */
+  int32_t row_floats;
+  int32_t reserved;
+} gsr_gather_table;
+GSR_API int gsr_compact_scratch_bytes(int32_t P, size_t* bytes);
+GSR_API int gsr_compact_indices(int32_t P, const uint8_t* mask, int32_t* idx_out, int32_t add, int64_t* count_out,
+                                void* scratch, void* stream);
+GSR_API int gsr_gather_rows(int32_t n_tables, const gsr_gather_table* tables, int64_t n_rows, const int32_t* idx,
+                            void* stream);
+
 /* Data-parallel exchange over NVLink peer memory (gsr_dp.PeerExchange; no reference counterpart -- the reference
  * is single-GPU, the semantic is the batch sum of train_stacked_transformer.py:203-222 across ranks).
  * gsr_peer_allreduce: in-place SUM over `world` ranks of n_floats floats (a multiple of 4).  peer_ptrs[p] = address, in
