@@ -9,14 +9,8 @@
 
 namespace gsr {
 
-// ||q||_2 as torch's norm reduction evaluates a row of 4 on this GPU: sqrt((x^2 + z^2) + (y^2 + w^2)) with every
-// product rounded (established by trying all summation trees against torch.linalg.vector_norm on a B200: this is
-// the only family that matches bit for bit; tests/test_gpu_activations.py keeps checking it).
-__device__ __forceinline__ float quat_norm(float4 q) {
-  return __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(q.x, q.x), __fmul_rn(q.z, q.z)),
-                              __fadd_rn(__fmul_rn(q.y, q.y), __fmul_rn(q.w, q.w))));
-}
-
+// (quat_norm / act_sigmoid / act_normalize live in common.cuh: preprocess_fwd / preprocess_bwd apply the same
+// expressions in place when the rasterizer is handed the raw parameters, gsr_inputs.raw_params.)
 __global__ void __launch_bounds__(256) activate_kernel(int P, const float* __restrict__ opacity_raw,
                                                        const float* __restrict__ scaling_raw,
                                                        const float4* __restrict__ rotation_raw,
@@ -25,12 +19,10 @@ __global__ void __launch_bounds__(256) activate_kernel(int P, const float* __res
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= P) return;
   const size_t I = (size_t)i;
-  opacities[I] = __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-__ldg(opacity_raw + I))));
+  opacities[I] = act_sigmoid(__ldg(opacity_raw + I));
 #pragma unroll
   for (int k = 0; k < 3; k++) scales[3 * I + k] = expf(__ldg(scaling_raw + 3 * I + k));
-  const float4 q = __ldg(rotation_raw + I);
-  const float n = fmaxf(quat_norm(q), 1e-12f);
-  rotations[I] = make_float4(__fdiv_rn(q.x, n), __fdiv_rn(q.y, n), __fdiv_rn(q.z, n), __fdiv_rn(q.w, n));
+  rotations[I] = act_normalize(__ldg(rotation_raw + I));
 }
 
 // Chain rule of the three activations; the activated values are recomputed from the raw parameters.

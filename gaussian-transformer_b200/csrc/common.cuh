@@ -173,6 +173,7 @@ struct Cam {
   const float* campos;
   float tanfovx, tanfovy, focal_x, focal_y, scale_modifier;
   int W, H, gx, gy;
+  int raw_params;  // opacities / scales / rotations are the RAW parameters: the kernels apply the activations
 };
 
 // ---------------------------------------------------------------- device helpers
@@ -231,6 +232,19 @@ __device__ __forceinline__ float gauss_power2(float2 m, float2 npix, float2 AC, 
   const float s = __fmaf_rn(d.x, p.x, t1);
   const float v = __fmul_rn(d.y, __fmul_rn(d.x, B));
   return __fmaf_rn(s, -0.5f, -v);
+}
+
+// The parameter activations of scene/gaussian_model.py:43-51,95-106 as torch's CUDA kernels evaluate them (bit for
+// bit on this GPU, tests/test_gpu_activations.py): sigmoid = 1 / (1 + expf(-x)), exp = expf,
+// F.normalize = x / max(||x||_2, 1e-12) with ||q||_2 = sqrt((x^2 + z^2) + (y^2 + w^2)), every product rounded.
+__device__ __forceinline__ float quat_norm(float4 q) {
+  return __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(q.x, q.x), __fmul_rn(q.z, q.z)),
+                              __fadd_rn(__fmul_rn(q.y, q.y), __fmul_rn(q.w, q.w))));
+}
+__device__ __forceinline__ float act_sigmoid(float x) { return __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-x))); }
+__device__ __forceinline__ float4 act_normalize(float4 q) {
+  const float n = fmaxf(quat_norm(q), 1e-12f);
+  return make_float4(__fdiv_rn(q.x, n), __fdiv_rn(q.y, n), __fdiv_rn(q.z, n), __fdiv_rn(q.w, n));
 }
 
 __device__ __forceinline__ float warp_sum(float v) {

@@ -152,6 +152,8 @@ int check_inputs(const gsr_inputs* in) {
     if (!in->scales || !in->rotations)
       return fail(GSR_ERR_INVALID, "either scales+rotations or cov3D_precomp is required");
     if (!aligned16(in->rotations)) return fail(GSR_ERR_INVALID, "rotations must be 16-byte aligned");
+  } else if (in->raw_params) {
+    return fail(GSR_ERR_INVALID, "raw_params needs scales + rotations (the raw _scaling / _rotation), not cov3D_precomp");
   }
   return GSR_OK;
 }
@@ -171,6 +173,7 @@ Cam make_cam(const gsr_inputs* in) {
   c.H = in->H;
   c.gx = (in->W + TILE - 1) / TILE;
   c.gy = (in->H + TILE - 1) / TILE;
+  c.raw_params = in->raw_params != 0;
   return c;
 }
 

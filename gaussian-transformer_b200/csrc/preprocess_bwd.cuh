@@ -113,12 +113,18 @@ __device__ __forceinline__ void geom_backward(size_t I, const float* __restrict_
   const float* __restrict__ proj = cam.proj;
   float c3[6];
   float q0 = 0.f, q1 = 0.f, q2 = 0.f, q3 = 0.f, s0 = 0.f, s1 = 0.f, s2 = 0.f;
+  float4 q_raw = make_float4(0.f, 0.f, 0.f, 0.f);
   if (cov3D_precomp != nullptr) {
 #pragma unroll
     for (int k = 0; k < 6; k++) c3[k] = __ldg(cov3D_precomp + 6 * I + k);
   } else {
     s0 = __ldg(scales + 3 * I); s1 = __ldg(scales + 3 * I + 1); s2 = __ldg(scales + 3 * I + 2);
-    const float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + I);
+    float4 q = __ldg(reinterpret_cast<const float4*>(rotations) + I);
+    q_raw = q;
+    if (cam.raw_params) {  // raw parameters in: the same activated values as the forward computed
+      s0 = expf(s0); s1 = expf(s1); s2 = expf(s2);
+      q = act_normalize(q);
+    }
     q0 = q.x; q1 = q.y; q2 = q.z; q3 = q.w;
     cov3d_from_scale_rot(s0, s1, s2, cam.scale_modifier, q0, q1, q2, q3, c3);
   }
@@ -227,6 +233,16 @@ __device__ __forceinline__ void geom_backward(size_t I, const float* __restrict_
             4 * y * (dMt[2][2] + dMt[0][0]);
     dq[3] = 2 * r * (dMt[0][1] - dMt[1][0]) + 2 * x * (dMt[2][0] + dMt[0][2]) + 2 * y * (dMt[1][2] + dMt[2][1]) -
             4 * z * (dMt[1][1] + dMt[0][0]);
+    if (cam.raw_params) {
+      // chain rule of exp and F.normalize (the autograd replay of gaussian_model.py:95-102, activations.cuh):
+      // d/ds_raw = g * exp(s_raw);  y = q / n: dq_raw = g / n - (n > eps ? y <y, g> / n : 0)
+      o.dscale[0] *= s0; o.dscale[1] *= s1; o.dscale[2] *= s2;
+      const float nr = quat_norm(q_raw);
+      const float inv = 1.0f / fmaxf(nr, 1e-12f);
+      const float dot = nr > 1e-12f ? (r * dq[0] + x * dq[1] + y * dq[2] + z * dq[3]) : 0.f;
+      dq[0] = (dq[0] - r * dot) * inv; dq[1] = (dq[1] - x * dot) * inv;
+      dq[2] = (dq[2] - y * dot) * inv; dq[3] = (dq[3] - z * dot) * inv;
+    }
   }
 }
 
@@ -384,7 +400,9 @@ __global__ void __launch_bounds__(PB_THREADS, 5) preprocess_bwd_staged_kernel(
     s_v3[2][3 * tid] = A.x; s_v3[2][3 * tid + 1] = A.y; s_v3[2][3 * tid + 2] = A.z;
 #pragma unroll
     for (int k = 0; k < 6; k++) s_cov[6 * tid + k] = o.dcov[k];
-    __stcs(out.dL_dopacity + I, A.w);
+    // raw parameters: sigmoid backward, grad * (1 - y) * y with y = the opacity the forward stored
+    const float op_ = __ldg(&g1[i].w);
+    __stcs(out.dL_dopacity + I, cam.raw_params ? A.w * (1.0f - op_) * op_ : A.w);
     __stcs(reinterpret_cast<float4*>(out.dL_dconic) + I, make_float4(B.z, B.w, 0.f, Cyy));
     __stcs(reinterpret_cast<float4*>(out.dL_drot) + I, make_float4(o.dq[0], o.dq[1], o.dq[2], o.dq[3]));
   }
@@ -422,7 +440,10 @@ __global__ void __launch_bounds__(PB_THREADS) preprocess_bwd_kernel(
   float Cyy = acc.acc2[i];
   finish_2d_grads(__ldg(g1 + i), cam.W, cam.H, B, Cyy);  // opacity as the forward saw it
   out.dL_dcolors[3 * I] = A.x; out.dL_dcolors[3 * I + 1] = A.y; out.dL_dcolors[3 * I + 2] = A.z;
-  out.dL_dopacity[I] = A.w;
+  {
+    const float op_ = __ldg(&g1[i].w);
+    out.dL_dopacity[I] = cam.raw_params ? A.w * (1.0f - op_) * op_ : A.w;
+  }
   out.dL_dmeans2D[3 * I] = B.x; out.dL_dmeans2D[3 * I + 1] = B.y; out.dL_dmeans2D[3 * I + 2] = 0.f;
   out.dL_dconic[4 * I] = B.z; out.dL_dconic[4 * I + 1] = B.w; out.dL_dconic[4 * I + 2] = 0.f;
   out.dL_dconic[4 * I + 3] = Cyy;

@@ -223,6 +223,15 @@ __device__ __forceinline__ bool pre_geometry(int i, float px3, float py3, float 
   return true;
 }
 
+// gsr_inputs.raw_params: the kernel was handed _opacity / _scaling / _rotation (scene/gaussian_model.py:95-106) and
+// applies sigmoid / exp / normalize itself -- the values the separate activation pass would have written.
+__device__ __forceinline__ void apply_activations(float& opacity, float* sc, float4& q) {
+  opacity = act_sigmoid(opacity);
+#pragma unroll
+  for (int k = 0; k < 3; k++) sc[k] = expf(sc[k]);
+  q = act_normalize(q);
+}
+
 constexpr int PF_THREADS = 128;
 #ifndef GSR_PF_MIN_CTAS
 #define GSR_PF_MIN_CTAS 7
@@ -289,6 +298,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(
   float m[3] = {0.f, 0.f, 0.f}, sc[3] = {0.f, 0.f, 0.f};
   load_mean_scale<STAGE_IN, 256>(P, base, tid, means3D, scales, s_mean, s_scale, m, sc);
   if (i >= P) return;
+  if (cam.raw_params) apply_activations(opac_in, sc, q_in);
   int out_radius = 0, tiles = 0;
   float4 o0 = make_float4(0.f, 0.f, 0.f, 0.f), o1 = o0, o2 = o0;
   float conx, cony, conz;
@@ -368,6 +378,7 @@ __global__ void __launch_bounds__(PF_THREADS, GSR_PF_MIN_CTAS) preprocess_fwd_st
 #endif
   float m[3] = {0.f, 0.f, 0.f}, sc[3] = {0.f, 0.f, 0.f};
   load_mean_scale<STAGE_IN, PF_THREADS>(P, base, tid, means3D, scales, s_mean, s_scale, m, sc);
+  if (cam.raw_params) apply_activations(opac_in, sc, q_in);
   int out_radius = 0, tiles = 0;
   float4 o0 = make_float4(0.f, 0.f, 0.f, 0.f), o1 = o0, o2 = o0;
   float conx = 0.f, cony = 0.f, conz = 0.f;

@@ -44,7 +44,7 @@ def _ptr(t):
 
 
 def _inputs(P, D, M, W, H, tanfovx, tanfovy, scale_modifier, prefiltered, debug, bg, means3D, sh, colors,
-            opacity, scales, rotations, cov3D, view, proj, campos, sh_rest=None):
+            opacity, scales, rotations, cov3D, view, proj, campos, sh_rest=None, raw_params=False):
     a = _lib.gsr_inputs()
     a.P, a.D, a.M, a.W, a.H = P, D, M, W, H
     a.tanfovx, a.tanfovy, a.scale_modifier = tanfovx, tanfovy, scale_modifier
@@ -53,6 +53,7 @@ def _inputs(P, D, M, W, H, tanfovx, tanfovy, scale_modifier, prefiltered, debug,
     a.opacities, a.scales, a.rotations, a.cov3D_precomp = _ptr(opacity), _ptr(scales), _ptr(rotations), _ptr(cov3D)
     a.viewmatrix, a.projmatrix, a.campos = _ptr(view), _ptr(proj), _ptr(campos)
     a.sh_rest = _ptr(sh_rest)
+    a.raw_params = int(bool(raw_params))
     return a
 
 
@@ -77,11 +78,13 @@ _r_hint = {}  # (device index, P, W, H) -> recent num_rendered (sizes the specul
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                         viewmatrix, projmatrix, tan_fovx, tan_fovy, image_height, image_width, sh, degree, campos,
-                        prefiltered, debug, sh_rest=None):
+                        prefiltered, debug, sh_rest=None, raw_params=False):
     """-> (num_rendered, out_color (3,H,W), radii (P,) int32, geomBuffer, binningBuffer, imgBuffer).
 
     sh_rest (extension): split SH storage -- `sh` is features_dc (P,1,3) and sh_rest features_rest (P,M-1,3), read
-    in place instead of through the torch.cat of scene/gaussian_model.py:108-111 (see split_sh_ok)."""
+    in place instead of through the torch.cat of scene/gaussian_model.py:108-111 (see split_sh_ok).
+    raw_params (extension): opacity / scales / rotations are the raw _opacity / _scaling / _rotation; the kernels
+    apply sigmoid / exp / normalize (gaussian_model.py:95-106) themselves."""
     _check_means(means3D)
     dev = means3D.device
     P, H, W = means3D.size(0), int(image_height), int(image_width)
@@ -97,7 +100,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         t = [_f32(x, dev) for x in (background, means3D, sh, colors, opacity, scales, rotations, cov3D_precomp,
                                     viewmatrix, projmatrix, campos)]
         args = _inputs(P, int(degree), M, W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier), prefiltered,
-                       debug, *t, sh_rest=sh_rest)
+                       debug, *t, sh_rest=sh_rest, raw_params=raw_params)
         gb, _, ib, _ = _lib.scratch_bytes(P, 0, W, H)
         geom, image = torch.empty(gb, **u8), torch.empty(ib, **u8)
         radii = torch.empty(P, dtype=torch.int32, device=dev)
@@ -133,7 +136,7 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy, dL_dout_color, sh,
                                  degree, campos, geomBuffer, R, binningBuffer, imageBuffer, debug, sh_grad=True,
-                                 factor_sink=None, out=None, sh_rest=None, debug_out=None):
+                                 factor_sink=None, out=None, sh_rest=None, debug_out=None, raw_params=False):
     """-> (dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations).
 
     sh_grad=False (extension, used by gsr_dp): dL_dsh is not computed and returned as None; the caller rebuilds it
@@ -144,7 +147,9 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     into the caller's tensors (same shape, float32, contiguous) instead of freshly allocated ones.  sh_rest
     (extension): split SH storage as in rasterize_gaussians; dL_dsh is then the pair (dL_dfeatures_dc (P,1,3),
     dL_dfeatures_rest (P,M-1,3)).  debug_out (test hook): a dict that receives "conic" = dL_dconic (P,2,2) and
-    "work" = the backward scratch buffer; nothing is retained otherwise."""
+    "work" = the backward scratch buffer; nothing is retained otherwise.  raw_params (extension): scales /
+    rotations are the raw parameters and dL_dopacity / dL_dscales / dL_drotations are the gradients of the RAW
+    parameters (the activations' chain rule is folded into preprocess_bwd)."""
     _check_means(means3D)
     dev = means3D.device
     P = means3D.size(0)
@@ -172,7 +177,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
             # opacities are not needed by backward (they live in geomBuffer); pass a valid pointer for the checker
             t[4] = t[1]
             args = _inputs(P, int(degree), M, W, H, float(tan_fovx), float(tan_fovy), float(scale_modifier), False,
-                           debug, *t, sh_rest=sh_rest)
+                           debug, *t, sh_rest=sh_rest, raw_params=raw_params)
             dpix = _f32(dL_dout_color, dev)
             _, _, _, wb = _lib.scratch_bytes(P, int(R), W, H)
             work = torch.empty(wb, dtype=torch.uint8, device=dev)

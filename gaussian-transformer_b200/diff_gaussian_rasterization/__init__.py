@@ -81,7 +81,7 @@ def _take_out():
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp, settings,
-                sh_rest=None):
+                sh_rest=None, raw_params=False):
         s = settings
         call = (s.bg, means3D, colors_precomp, opacities, scales, rotations, s.scale_modifier, cov3Ds_precomp,
                 s.viewmatrix, s.projmatrix, s.tanfovx, s.tanfovy, s.image_height, s.image_width, sh, s.sh_degree,
@@ -90,12 +90,14 @@ class _RasterizeGaussians(torch.autograd.Function):
                          "\nAn error occured in forward. Please forward snapshot_fw.dump for debugging.") \
             if s.debug else None
         try:
-            num_rendered, color, radii, geom, binning, img = _C.rasterize_gaussians(*call, sh_rest=sh_rest)
+            num_rendered, color, radii, geom, binning, img = _C.rasterize_gaussians(*call, sh_rest=sh_rest,
+                                                                                    raw_params=raw_params)
         except Exception:
             if dump:
                 dump()
             raise
         ctx.raster_settings = s
+        ctx.raw_params = bool(raw_params)
         ctx.num_rendered = num_rendered
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning,
                               img, sh_rest)
@@ -119,7 +121,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         try:
             (g_means2D, g_colors, g_opac, g_means3D, g_cov3D, g_sh, g_scales,
              g_rot) = _C.rasterize_gaussians_backward(*call, sh_grad=sink is None, factor_sink=sink, out=_take_out(),
-                                                      sh_rest=sh_rest)
+                                                      sh_rest=sh_rest, raw_params=ctx.raw_params)
         except Exception:
             if dump:
                 dump()
@@ -128,21 +130,26 @@ class _RasterizeGaussians(torch.autograd.Function):
         if sh_rest is not None:
             g_sh, g_rest = g_sh if g_sh is not None else (None, None)
         # order of forward's inputs; the settings tuple gets None (DGR __init__.py:143-153)
-        return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None, g_rest
+        return g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None, g_rest, None
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
-                        raster_settings):
+                        raster_settings, raw_params=False):
     """`sh` may also be the pair (features_dc (P,1,3), features_rest (P,M-1,3)) of scene/gaussian_model.py:108-111:
-    the kernels then read (and write the gradients of) the two arrays in place instead of their torch.cat."""
+    the kernels then read (and write the gradients of) the two arrays in place instead of their torch.cat.
+    raw_params=True (extension): `opacities`, `scales`, `rotations` are the model's raw `_opacity`, `_scaling`,
+    `_rotation`; sigmoid / exp / normalize (gaussian_model.py:95-106) run inside preprocess_fwd and their chain rule
+    inside preprocess_bwd, so the returned gradients are those of the raw parameters."""
+    if raw_params and (scales is None or rotations is None or scales.numel() == 0 or rotations.numel() == 0):
+        raise Exception('raw_params needs the raw scale/rotation pair (not a precomputed 3D covariance)')
     if isinstance(sh, (tuple, list)):
         dc, rest = sh
         if _C.split_sh_ok(dc, rest):
             return _RasterizeGaussians.apply(means3D, means2D, dc, colors_precomp, opacities, scales, rotations,
-                                             cov3Ds_precomp, raster_settings, rest)
+                                             cov3Ds_precomp, raster_settings, rest, raw_params)
         sh = torch.cat((dc, rest), dim=1)
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, raster_settings)
+                                     cov3Ds_precomp, raster_settings, None, raw_params)
 
 
 class GaussianRasterizer(nn.Module):
@@ -157,7 +164,7 @@ class GaussianRasterizer(nn.Module):
             return _C.mark_visible(positions, s.viewmatrix, s.projmatrix)
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None, rotations=None,
-                cov3D_precomp=None):
+                cov3D_precomp=None, raw_params=False):
         # same validation and messages as DGR __init__.py:191-195
         if (shs is None) == (colors_precomp is None):
             raise Exception('Please provide excatly one of either SHs or precomputed colors!')
@@ -167,4 +174,4 @@ class GaussianRasterizer(nn.Module):
         empty = torch.Tensor([])  # "absent" marker, as in the reference (:197-207)
         pick = lambda t: empty if t is None else t
         return rasterize_gaussians(means3D, means2D, pick(shs), pick(colors_precomp), opacities, pick(scales),
-                                   pick(rotations), pick(cov3D_precomp), self.raster_settings)
+                                   pick(rotations), pick(cov3D_precomp), self.raster_settings, raw_params)

@@ -21,6 +21,7 @@ class gsr_inputs(ctypes.Structure):
         ("colors_precomp", ctypes.c_void_p), ("opacities", ctypes.c_void_p), ("scales", ctypes.c_void_p),
         ("rotations", ctypes.c_void_p), ("cov3D_precomp", ctypes.c_void_p), ("viewmatrix", ctypes.c_void_p),
         ("projmatrix", ctypes.c_void_p), ("campos", ctypes.c_void_p), ("sh_rest", ctypes.c_void_p),
+        ("raw_params", ctypes.c_int32),
     ]
 
 

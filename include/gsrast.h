@@ -77,6 +77,11 @@ typedef struct gsr_inputs {
    * (P,M-1,3) and concatenates them for every render): when sh_rest is non-NULL, `sh` is the DC array and sh_rest
    * the rest; M is still the total number of coefficients.  NULL = `sh` is the concatenated (P,M,3) array. */
   const float* sh_rest;
+  /* Extension: non-zero = opacities / scales / rotations are the RAW parameters _opacity /
+   * _scaling / _rotation of scene/gaussian_model.py:95-106; preprocess_fwd applies sigmoid / exp / normalize itself
+   * (bit-identical to torch's kernels) and the backward returns the gradients of the RAW parameters (the chain rule
+   * is folded into preprocess_bwd) -- no separate activation pass in either direction.  Requires scales + rotations. */
+  int32_t raw_params;
 } gsr_inputs;
 
 /* Library version (major*10000 + minor*100 + patch) and the SM architecture the
