@@ -155,6 +155,53 @@ def cpu_baseline(sc, dpix):
             "sample": "1 full fwd+bwd iteration of the same workload (oracle/oracle.c, OpenMP), %.1f s" % dt}
 
 
+def cpu_baseline_pytorch(dev):
+    """BASELINE.json's second baseline and configs[0]: the pure-PyTorch CPU implementation of rasterize_gaussians
+    (oracle/torch_cpu_rasterizer.py, autograd backward) on config C1 -- the bundled tiramisu_ds COLMAP points as
+    Gaussians, 800x450 -- one forward+backward on all host cores; next to it this library on the same scene."""
+    import torch
+    import gsr_scenes as S
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import torch_cpu_rasterizer as T
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    sc = S.scene_C1(os.path.join(ROOT, "tests", "golden", "data", "c1_tiramisu_points.npz"))
+    dpix_np = S.upstream_grad(sc["W"], sc["H"], 1)
+    torch.set_num_threads(os.cpu_count() or 1)
+    t0 = time.time()
+    color_cpu, _, _, info = T.fwd_bwd(sc, dpix_np)
+    dt = time.time() - t0
+    t = {k: torch.from_numpy(np.ascontiguousarray(sc[k])).to(dev) for k in TENSORS}
+    dpix = torch.from_numpy(dpix_np).to(dev)
+    raster = GaussianRasterizer(GaussianRasterizationSettings(
+        sc["H"], sc["W"], sc["tanfovx"], sc["tanfovy"], t["bg"], 1.0, t["viewmatrix"], t["projmatrix"],
+        sc["sh_degree"], t["campos"], False, False))
+
+    def one():
+        leaves = {k: t[k].detach().requires_grad_(True) for k in LEAVES}
+        color, _ = raster(means3D=leaves["means3D"], means2D=torch.zeros_like(leaves["means3D"]),
+                          opacities=leaves["opacities"], shs=leaves["sh"], scales=leaves["scales"],
+                          rotations=leaves["rotations"])
+        color.backward(dpix)
+        return color
+    for _ in range(5):
+        color = one()
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(50):
+        one()
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / 50
+    return {"value": 1.0 / dt, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
+            "implementation": "pure PyTorch fp32 on the CPU, autograd backward (oracle/torch_cpu_rasterizer.py)",
+            "sample": "1 fwd+bwd of config C1 (33,730 COLMAP points as Gaussians, SH3, 800x450, %d instances), %.1f s"
+                      % (info["num_rendered"], dt),
+            "this_library_same_scene": {"value": 1000.0 / ms, "unit": UNIT, "ms_per_step": ms,
+                                        "max_abs_image_diff_vs_pytorch": float(
+                                            (color.detach().cpu() - color_cpu).abs().max())}}
+
+
 def run_reference(args, rank, world):
     """Reference arm: the UNMODIFIED reference rasterizer (oracle/_ref, its own CUDA kernels) on the same box and
     workload; if that library is absent, the CPU oracle port."""
@@ -557,6 +604,7 @@ def run_ours(args, rank, world, local_rank):
         line["c3"] = c3
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(sc, dpix_np)
+        line["cpu_baseline_pytorch"] = cpu_baseline_pytorch(dev)
     return line
 
 

@@ -88,14 +88,21 @@ constexpr int SORT_TILE_KEYS = 256 * GSR_SORT_ROUNDS;  // keys per CTA in depth_
 inline size_t sort_ctas(size_t P) { return (P + SORT_TILE_KEYS - 1) / SORT_TILE_KEYS; }
 // onesweep.cuh: 4096 keys per tile; scratch words = [4][256] digit histograms, 64 words of tile counters,
 // [4][tiles + groups][256] look-back status words
-#ifndef GSR_OS_KPT
-#define GSR_OS_KPT 16
-#endif
-constexpr int OS_TILE_KEYS = 256 * GSR_OS_KPT;
-inline size_t os_tiles(size_t n) { return (n + OS_TILE_KEYS - 1) / OS_TILE_KEYS; }
+// onesweep.cuh: tiles of 256 threads x 16 keys (4096), or x 4 keys (1024) for inputs of at most OS_SMALL_N keys
+// (small scenes: more, shorter tiles -- the pass is latency bound there).  Scratch words = [4][256] digit histograms,
+// 64 words of tile counters, [4][tiles + groups][256] look-back status words
+constexpr size_t OS_SMALL_N = 131072;
 constexpr int OS_GROUP_TILES = 16;
+inline int os_kpt(size_t n) { return n <= OS_SMALL_N ? 4 : 16; }
+inline size_t os_tiles(size_t n) { const size_t t = 256 * (size_t)os_kpt(n); return (n + t - 1) / t; }
 inline size_t os_groups(size_t n) { return (os_tiles(n) + OS_GROUP_TILES - 1) / OS_GROUP_TILES; }
-inline size_t os_scratch_words(size_t n) { return 4 * 256 + 64 + 4 * (os_tiles(n) + os_groups(n)) * 256; }
+inline size_t os_scratch_words(size_t n) {
+  // both tilings' needs are covered for any n (the small tiling only ever sees n <= OS_SMALL_N)
+  const size_t small_n = n < OS_SMALL_N ? n : OS_SMALL_N;
+  const size_t a = (n + 4095) / 4096, b = (small_n + 1023) / 1024;
+  const size_t t = a > b ? a : b;
+  return 4 * 256 + 64 + 4 * (t + (t + OS_GROUP_TILES - 1) / OS_GROUP_TILES + 1) * 256;
+}
 // words of sort scratch behind keys / vals: whichever of the two sorts needs more
 inline size_t sort_scratch_words(size_t P) {
   const size_t a = 256 * (sort_ctas(P) + 1), b = os_scratch_words(P);

@@ -21,15 +21,9 @@ namespace gsr {
 
 constexpr int OS_THREADS = 256;
 constexpr int OS_WARPS = OS_THREADS / 32;
-#ifndef GSR_OS_KPT
-#define GSR_OS_KPT 16
-#endif
 #ifndef GSR_OS_MATCH
 #define GSR_OS_MATCH 0
 #endif
-constexpr int OS_KPT = GSR_OS_KPT;                // keys per thread
-constexpr int OS_TILE = OS_THREADS * OS_KPT;      // 4096 keys per tile
-constexpr int OS_SEG = 32 * OS_KPT;               // 512 consecutive keys per warp
 #ifndef GSR_OS_LOOKBACK
 #define GSR_OS_LOOKBACK 16
 #endif
@@ -39,7 +33,6 @@ constexpr uint32_t OS_FLAG_AGG = 1u << 30;        // status word = count | flag:
 constexpr uint32_t OS_FLAG_INC = 2u << 30;        //                             inclusive prefix over tiles 0..t
 constexpr uint32_t OS_COUNT_MASK = (1u << 30) - 1u;
 
-static_assert(OS_TILE == OS_TILE_KEYS, "scratch sizing (common.cuh) and the sort disagree");
 
 // lanes of `act` whose 8-bit digit equals this lane's: eight ballots (ALU pipe) instead of one MATCH.ANY (MIO pipe,
 // low throughput)
@@ -122,6 +115,8 @@ __global__ void __launch_bounds__(OS_THREADS) os_hist_kernel(const uint32_t* __r
 
 // One pass.  vals_in == nullptr: value = index (first pass).  hist = this pass's 256 digit totals, counter = this
 // pass's tile counter (zeroed), status / gstatus = this pass's [tiles][256] / [groups][256] look-back words (zeroed).
+// OS_KPT keys per thread: a tile is 256 * OS_KPT keys, a warp owns 32 * OS_KPT consecutive ones.
+template <int OS_KPT>
 __global__ void __launch_bounds__(OS_THREADS) os_pass_kernel(const uint32_t* __restrict__ keys_in,
                                                             const uint32_t* __restrict__ vals_in, int n, int shift,
                                                             const uint32_t* __restrict__ hist,
@@ -130,6 +125,7 @@ __global__ void __launch_bounds__(OS_THREADS) os_pass_kernel(const uint32_t* __r
                                                             uint32_t* __restrict__ gstatus,
                                                             uint32_t* __restrict__ keys_out,
                                                             uint32_t* __restrict__ vals_out) {
+  constexpr int OS_TILE = OS_THREADS * OS_KPT, OS_SEG = 32 * OS_KPT;
   __shared__ uint32_t cnt[OS_WARPS][256];  // per-warp digit counts, then per-warp running positions in the tile
   __shared__ uint32_t s_scan[16], s_delta[256];
   __shared__ uint32_t s_keys[OS_TILE], s_vals[OS_TILE];
@@ -260,11 +256,16 @@ inline int os_sort_launch(uint32_t* const keys[2], uint32_t* const vals[2], int 
   os_hist_kernel<<<hist_ctas, OS_THREADS, 0, stream>>>(keys[0], n, hist);
   for (int pass = 0; pass < 4; pass++) {
     const int src = pass & 1, dst = src ^ 1;
-    os_pass_kernel<<<tiles, OS_THREADS, 0, stream>>>(keys[src], pass == 0 ? nullptr : vals[src], n, 8 * pass,
-                                                     hist + 256 * pass, counters + pass,
-                                                     status + pass * per_pass,
-                                                     status + pass * per_pass + (size_t)tiles * 256, keys[dst],
-                                                     vals[dst]);
+    const uint32_t* vin = pass == 0 ? nullptr : vals[src];
+    uint32_t* st = status + pass * per_pass;
+    if (os_kpt((size_t)n) == 4)
+      os_pass_kernel<4><<<tiles, OS_THREADS, 0, stream>>>(keys[src], vin, n, 8 * pass, hist + 256 * pass,
+                                                          counters + pass, st, st + (size_t)tiles * 256, keys[dst],
+                                                          vals[dst]);
+    else
+      os_pass_kernel<16><<<tiles, OS_THREADS, 0, stream>>>(keys[src], vin, n, 8 * pass, hist + 256 * pass,
+                                                           counters + pass, st, st + (size_t)tiles * 256, keys[dst],
+                                                           vals[dst]);
   }
   return 5;
 }
