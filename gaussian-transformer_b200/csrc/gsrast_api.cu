@@ -111,6 +111,7 @@ int env_switch(const char* name, int dflt) {
 }
 std::atomic<int> g_force_bin_cta{env_switch("GSR_BIN_CTA", -1)};  // -1 = by list size, 0 / 1 = forced
 std::atomic<int> g_render_bwd{env_switch("GSR_RENDER_BWD", 2)};   // 1 = one pixel per thread, 2 = two (default)
+std::atomic<int> g_render_fwd{env_switch("GSR_RENDER_FWD", 2)};   // 1 = one pixel per thread, 2 = two (default)
 std::atomic<int> g_sort{env_switch("GSR_SORT", 1)};               // 1 = onesweep.cuh (default), 0 = depth_sort.cuh
 std::atomic<long long> g_launches{0};                             // kernels launched by this library (gsr_launch_count)
 #define GSR_LAUNCHED(n) g_launches.fetch_add((n), std::memory_order_relaxed)
@@ -189,8 +190,18 @@ int gsr_set_option(const char* name, int32_t value) {
   if (!name) return fail(GSR_ERR_INVALID, "gsr_set_option: NULL name");
   if (!strcmp(name, "bin_cta")) g_force_bin_cta.store(value < 0 ? -1 : (value != 0));
   else if (!strcmp(name, "sort")) g_sort.store(value != 0);
+  else if (!strcmp(name, "render_fwd")) g_render_fwd.store(value == 1 ? 1 : 2);
   else if (!strcmp(name, "render_bwd")) g_render_bwd.store(value == 1 || value == 3 ? value : 2);
   else return fail(GSR_ERR_INVALID, std::string("gsr_set_option: unknown option ") + name);
+  return GSR_OK;
+}
+
+int gsr_selftest_expf(uint32_t lo_bits, uint32_t hi_bits, uint64_t* mismatches_device, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (!mismatches_device || hi_bits < lo_bits) return fail(GSR_ERR_INVALID, "gsr_selftest_expf: bad arguments");
+  GSR_CUDA(cudaMemsetAsync(mismatches_device, 0, 8, stream), "selftest memset");
+  expf_selftest_kernel<<<148 * 8, 256, 0, stream>>>(lo_bits, hi_bits, (unsigned long long*)mismatches_device), GSR_LAUNCHED(1);
+  GSR_STAGE("expf_selftest", 0, stream);
   return GSR_OK;
 }
 
@@ -423,10 +434,15 @@ int forward_post_impl(const gsr_inputs* in, const void* geom, void* binning, voi
     }
   }
   ScopedStage prof_(GSR_STAGE_RENDER_FWD, stream);
-  dim3 grid(cam.gx, cam.gy), block(TILE_PIX);
-  render_fwd_kernel<<<grid, block, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, g.g0, g.g1, g.g2,
-                                                in->colors_precomp, in->bg, im.final_T, im.n_contrib, out_color,
-                                                guard, cap), GSR_LAUNCHED(1);
+  dim3 grid(cam.gx, cam.gy);
+  if (g_render_fwd.load(std::memory_order_relaxed) == 1)
+    render_fwd_kernel<<<grid, TILE_PIX, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, g.g0, g.g1, g.g2,
+                                                     in->colors_precomp, in->bg, im.final_T, im.n_contrib, out_color,
+                                                     guard, cap), GSR_LAUNCHED(1);
+  else
+    render_fwd2_kernel<<<grid, RF2_THREADS, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, g.g0, g.g1, g.g2,
+                                                         in->colors_precomp, in->bg, im.final_T, im.n_contrib,
+                                                         out_color, guard, cap), GSR_LAUNCHED(1);
   GSR_STAGE("render_fwd", in->debug, stream);
   return GSR_OK;
 }

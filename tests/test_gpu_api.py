@@ -425,3 +425,35 @@ def test_launch_counter_counts_kernels():
     n_all = _lib.launch_count(reset=True)
     assert 4 <= n_fwd <= 24 and n_fwd + 2 <= n_all <= n_fwd + 4, (n_fwd, n_all)
     assert _lib.launch_count() == 0
+
+
+def test_packed_expf_is_bit_identical_to_expf():
+    """render_fwd2_kernel evaluates exp() for its two pixels with a hand-scheduled copy of nvcc's expf sequence (so
+    that half of it packs into FFMA2 / FADD2 / FMUL2).  n_contrib and final_T are bit-exact contracts, so the copy
+    must return expf's bits: every float in [-104, -1e-30] and [1e-30, 104] (by bit pattern) and their negations."""
+    import struct
+    from diff_gaussian_rasterization import _lib
+    bits = lambda f: struct.unpack("<I", struct.pack("<f", f))[0]
+    out = torch.zeros(1, dtype=torch.int64, device="cuda")
+    for lo, hi in ((bits(1e-30), bits(104.0)), (0, 4096), (bits(104.0), bits(1e30))):
+        _lib.check(_lib.lib.gsr_selftest_expf(lo, hi, out.data_ptr(), torch.cuda.current_stream().cuda_stream))
+        torch.cuda.synchronize()
+        assert int(out.item()) == 0, (hex(lo), hex(hi), int(out.item()))
+
+
+def test_two_pixel_forward_equals_one_pixel_forward():
+    from diff_gaussian_rasterization import _lib
+    from util import ours_forward
+    for name in ("s_deg3", "s_big", "s_dense_opaque", "nonfinite", "one_huge", "s_huge_lists"):
+        sc, _ = cases.case(name)
+        d = to_device(sc)
+        res = []
+        for v in (1, 2):
+            _lib.set_option("render_fwd", v)
+            res.append(ours_forward(d))
+        _lib.set_option("render_fwd", 2)
+        a, b = res
+        assert torch.equal(a["n_contrib"], b["n_contrib"]), name
+        assert torch.equal(a["final_T"].view(torch.int32), b["final_T"].view(torch.int32)), name
+        c1, c2 = a["color"], b["color"]
+        assert torch.equal(torch.nan_to_num(c1), torch.nan_to_num(c2)) and torch.equal(c1.isnan(), c2.isnan()), name
