@@ -281,7 +281,7 @@ __device__ __forceinline__ float rcp_approx(float x) {
 // counts, in counters[0..2], the accepted (pixel, Gaussian) pairs, the pairs the forward accepted but this kernel's
 // ex2.approx alpha rejects, and the reverse (defined deviation 4).
 template <bool COUNT>
-__global__ void __launch_bounds__(RB2_THREADS, COUNT ? 4 : 6) render_bwd2_kernel(
+__global__ void __launch_bounds__(RB2_THREADS, COUNT ? 4 : 8) render_bwd2_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
     const float* __restrict__ bg, const float4* __restrict__ g0, const float4* __restrict__ g1,
     const float4* __restrict__ g2, const float* __restrict__ colors_precomp, const float* __restrict__ final_T,

@@ -48,7 +48,9 @@ class FusedAdam(torch.optim.Optimizer):
                 if p.grad.is_sparse:
                     raise RuntimeError("FusedAdam does not support sparse gradients")
                 if not p.is_contiguous():
-                    raise RuntimeError("FusedAdam: parameters must be contiguous")
+                    # e.g. _xyz built from a transposed numpy array (scene/dataset_readers.py:107-115 fetchPly): give
+                    # the parameter dense storage once; the Parameter object (and every reference to it) stays
+                    p.data = p.data.contiguous()
                 st = self.state[p]
                 if len(st) == 0:
                     st["step"] = torch.tensor(0.0, dtype=torch.float32)  # torch's layout: a CPU scalar tensor

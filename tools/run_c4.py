@@ -91,6 +91,10 @@ def main():
     ap.add_argument("--stack", choices=["b200", "reference"], default="b200")
     ap.add_argument("--iterations", type=int, default=3000)
     ap.add_argument("--work", default=os.path.join(ROOT, "gpurun_out", "c4"))
+    ap.add_argument("--fused", action="store_true",
+                    help="b200 stack + the optional trainer-side changes of INTEGRATION.md sections 6-9, applied by "
+                         "patching the imported modules (train.py itself stays byte-identical): FusedAdam, "
+                         "gsr_render.render (raw parameters + split SH), gsr_densify, fused densification statistics")
     ap.add_argument("--dataset-only", action="store_true", help="write the dataset (CPU) and stop")
     ap.add_argument("--profile", default=None, help="dev: run under torch.profiler and write the kernel / CPU-op tables "
                                                     "to this file (the timing of such a run is not a result)")
@@ -131,8 +135,42 @@ def main():
         torch.cuda.synchronize()
         marks["t0"], marks["P0"] = time.perf_counter(), int(self.get_xyz.shape[0])
     gm.GaussianModel.training_setup = timed_setup
+    hits = {"calls": 0, "misses": 0}
+    if args.stack == "b200":
+        # hit rate of the speculative forward (phase 2 launched before num_rendered reaches the host): a miss is a
+        # call whose binning buffer had to be re-allocated, i.e. gsr_forward_post ran a second time
+        from diff_gaussian_rasterization import _lib
+        post = _lib.lib.gsr_forward_post
+        fwd = _lib.lib.gsr_forward
 
-    out = os.path.join(os.path.abspath(args.work), "out_" + args.stack)
+        def count_post(*a):
+            hits["misses"] += 1
+            return post(*a)
+
+        def count_fwd(*a):
+            hits["calls"] += 1
+            return fwd(*a)
+        _lib.lib.gsr_forward_post, _lib.lib.gsr_forward = count_post, count_fwd
+    if args.fused:
+        if args.stack != "b200":
+            sys.exit("--fused needs --stack b200")
+        import gaussian_renderer
+        import gsr_densify
+        import gsr_optim
+        import gsr_render
+        inner = gm.GaussianModel.training_setup
+
+        def fused_setup(self, opt):
+            inner(self, opt)
+            groups = [{"params": g["params"], "lr": g["lr"], "name": g["name"]} for g in self.optimizer.param_groups]
+            self.optimizer = gsr_optim.FusedAdam(groups, lr=0.0, eps=1e-15)
+        gm.GaussianModel.training_setup = fused_setup
+        gaussian_renderer.render = gsr_render.render                                  # section 7
+        gm.GaussianModel.densify_and_prune = gsr_densify.densify_and_prune            # section 9
+        gm.GaussianModel.prune_points = gsr_densify.prune_points
+
+
+    out = os.path.join(os.path.abspath(args.work), "out_" + args.stack + ("_fused" if args.fused else ""))
     shutil.rmtree(out, ignore_errors=True)
     sys.argv = ["train.py", "-s", ds, "-m", out, "--iterations", str(args.iterations), "--test_iterations", "-1",
                 "--save_iterations", str(args.iterations), "--quiet"]
@@ -156,7 +194,11 @@ def main():
     final = PlyData.read(ply)["vertex"]
     print(json.dumps({
         "workload": "C4: reference train.py unmodified, table_ds points + synthetic orbit poses, default 1.6K rescale",
-        "stack": args.stack, "iterations": args.iterations, "loop_s": round(sec, 3),
+        "stack": args.stack + (" + FusedAdam, gsr_render (raw parameters, split SH), gsr_densify" if args.fused else ""),
+        "speculative_forward": ({"calls": hits["calls"], "misses": hits["misses"],
+                                 "hit_rate": round(1.0 - hits["misses"] / max(hits["calls"], 1), 4)}
+                                if args.stack == "b200" else None),
+        "iterations": args.iterations, "loop_s": round(sec, 3),
         "iters_per_s": round(args.iterations / sec, 2), "cameras": n_cams, "P_start": marks["P0"],
         "P_final": int(final.count), "ply_properties": len(final.properties),
         "modules": {"rasterizer": os.path.relpath(dgr.__file__, ROOT), "simple_knn": os.path.relpath(knn.__file__, ROOT),
