@@ -73,7 +73,8 @@ template <bool SCATTER>
 __device__ __forceinline__ void bin_walk(int begin, int end, int lane, uint32_t* tab, uint4* desc,
                                          const uint32_t* __restrict__ order, const uint2* __restrict__ rects,
                                          const float4* __restrict__ g0, int gx, int gy, int by0, int by1,
-                                         uint32_t* __restrict__ point_list) {
+                                         uint32_t* __restrict__ point_list, uint32_t list_cap = 0xffffffffu) {
+  (void)list_cap;
   const unsigned lt = (1u << lane) - 1u;
   for (int r0 = begin; r0 < end; r0 += 32) {
     const int k = r0 + lane;
@@ -114,16 +115,20 @@ __device__ __forceinline__ void bin_walk(int begin, int end, int lane, uint32_t*
         if (lane < nt) {
           const int ty = (int)(((uint32_t)lane * (e.z >> 16)) >> 10);
           const int idx = rowbase + ty * gx + (lane - ty * wdt);
+          GSR_CHECK(idx >= 0 && idx < (by1 - by0) * gx);
           const uint32_t v = tab[idx];
           tab[idx] = v + 1u;
+          GSR_CHECK(!SCATTER || v < list_cap);
           if (SCATTER) point_list[v] = e.x;
         }
       } else {
         for (int t = lane; t < nt; t += 32) {
           const int ty = t / wdt;
           const int idx = rowbase + ty * gx + (t - ty * wdt);
+          GSR_CHECK(idx >= 0 && idx < (by1 - by0) * gx);
           const uint32_t v = tab[idx];
           tab[idx] = v + 1u;
+          GSR_CHECK(!SCATTER || v < list_cap);
           if (SCATTER) point_list[v] = e.x;
         }
       }
@@ -160,7 +165,8 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_pass_kernel(int P, const u
   for (int t = lane; t < ntab; t += 32) tab[t] = SCATTER ? (__ldg(&ranges[tile0 + t].x) + row[t]) : 0u;
   __syncwarp();
   const int begin = chunk * plan.chunk, end = min(P, begin + plan.chunk);
-  bin_walk<SCATTER>(begin, end, lane, tab, desc, order, rects, g0, gx, gy, by0, by1, point_list);
+  bin_walk<SCATTER>(begin, end, lane, tab, desc, order, rects, g0, gx, gy, by0, by1, point_list,
+                    cap);
   if (!SCATTER) {
     __syncwarp();
     for (int t = lane; t < ntab; t += 32) row[t] = tab[t];
@@ -204,7 +210,8 @@ __global__ void __launch_bounds__(BIN_WARPS * 32) bin_scatter_cta_kernel(
     }
   }
   __syncthreads();
-  bin_walk<true>(begin, end, lane, tab, s_desc[w], order, rects, g0, gx, gy, by0, by1, point_list);
+  bin_walk<true>(begin, end, lane, tab, s_desc[w], order, rects, g0, gx, gy, by0, by1, point_list,
+                 cap);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -280,6 +287,7 @@ __global__ void __launch_bounds__(BINC_THREADS) bin_count_cta_kernel(int P, cons
       const int y0 = max((int)(r.y & 0xffff), by0) - by0, y1 = min((int)(r.y >> 16), by1) - by0;
       if (maxx > minx)
         for (int y = y0; y < y1; y++) {
+          GSR_CHECK(y >= 0 && y < by1 - by0 && minx >= 0 && maxx <= gx);
           atomicAdd(&s_tab[y * (gx + 1) + minx], 1u);
           atomicAdd(&s_tab[y * (gx + 1) + maxx], 0xffffffffu);
         }

@@ -183,6 +183,19 @@ struct Cam {
   int raw_params;  // opacities / scales / rotations are the RAW parameters: the kernels apply the activations
 };
 
+// Bounds-checked build (make checked: -DGSR_BOUNDS_CHECK -> lib/libgsrast_checked.so): every index into a
+// shared-memory table and every scattered global store of the binning / sort / staging code is checked and the
+// kernel traps on a violation.  compute-sanitizer is closed on the GPU pool this was developed on; running the small
+// parity cases against the checked library (GSR_LIB_PATH) is the substitute (profiles/r02_bounds_check.txt).
+#ifdef GSR_BOUNDS_CHECK
+#define GSR_CHECK(cond)        \
+  do {                         \
+    if (!(cond)) __trap();     \
+  } while (0)
+#else
+#define GSR_CHECK(cond) ((void)0)
+#endif
+
 // ---------------------------------------------------------------- device helpers
 // m[r]*x + m[4+r]*y + m[8+r]*z + m[12+r] with the rounding points of the
 // reference's compiled transformPoint4x3/4x4 (DGR/cuda_rasterizer/auxiliary.h:58-77;

@@ -135,6 +135,7 @@ __global__ void __launch_bounds__(GATHER_THREADS) gather_rows_kernel(const __gri
     const long long row = e / t.row_floats;
     const int col = (int)(e - row * t.row_floats);
     const int32_t s = __ldg((t.idx ? t.idx : idx) + row);
+    GSR_CHECK(s < 0x7fffffff);
     t.dst[e] = s >= 0 ? __ldg(t.src + (long long)s * t.row_floats + col) : 0.f;
   }
 }

@@ -200,6 +200,7 @@ __global__ void __launch_bounds__(OS_THREADS) os_pass_kernel(const uint32_t* __r
     const unsigned m = grp[k];
     if (m) {
       const uint32_t lp = cnt[w][d] + __popc(m & lt);
+      GSR_CHECK(lp < (uint32_t)OS_TILE);
       s_keys[lp] = key[k];
       s_vals[lp] = val[k];
     }
@@ -236,6 +237,7 @@ __global__ void __launch_bounds__(OS_THREADS) os_pass_kernel(const uint32_t* __r
     if (idx < n_tile) {
       const uint32_t kk = s_keys[idx];
       const uint32_t pos = (uint32_t)idx + s_delta[(kk >> shift) & 255u];
+      GSR_CHECK(pos < (uint32_t)n);
       keys_out[pos] = kk;
       vals_out[pos] = s_vals[idx];
     }
