@@ -394,8 +394,20 @@ def run_ours(args, rank, world, local_rank):
         keep = LEAVES if args.dp_exchange == "allreduce" else gsr_dp.SMALL_LEAVES
         peer = None
         if args.dp_exchange == "peer":
-            peer = gsr_dp.PeerExchange(world, P_GAUSS, {k: tuple(t[k].shape) for k in keep}, dev, rank, world,
-                                       use_multimem=args.multimem, gather=args.peer_gather)
+            # symmetric memory (peer mapping over NVLink) may be unavailable on a box: every rank must take the same
+            # path, so the ranks agree on the outcome and fall back to the NCCL factor exchange together
+            try:
+                peer = gsr_dp.PeerExchange(world, P_GAUSS, {k: tuple(t[k].shape) for k in keep}, dev, rank, world,
+                                           use_multimem=args.multimem, gather=args.peer_gather)
+                ok = torch.ones(1, device=dev)
+            except Exception as exc:  # noqa: BLE001
+                print("bench.py: peer exchange unavailable on rank %d (%s); using --dp-exchange factors" % (rank, exc),
+                      file=sys.stderr)
+                ok = torch.zeros(1, device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if float(ok) == 0.0:
+                peer, args.dp_exchange = None, "factors"
+        if peer is not None:
             flat = peer.flat
         else:
             flat = gsr_dp.FlatGrads({k: tuple(t[k].shape) for k in keep}, dev)

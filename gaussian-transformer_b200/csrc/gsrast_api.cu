@@ -112,6 +112,7 @@ int env_switch(const char* name, int dflt) {
 std::atomic<int> g_force_bin_cta{env_switch("GSR_BIN_CTA", -1)};  // -1 = by list size, 0 / 1 = forced
 std::atomic<int> g_render_bwd{env_switch("GSR_RENDER_BWD", 2)};   // 1 = one pixel per thread, 2 = two (default)
 std::atomic<int> g_render_fwd{env_switch("GSR_RENDER_FWD", 2)};   // 1 = one pixel per thread, 2 = two (default)
+std::atomic<int> g_pre_fwd{env_switch("GSR_PRE_FWD", 1)};         // 1 = one tile per CTA (default), 2 = persistent bulk-copy kernel
 std::atomic<int> g_sort{env_switch("GSR_SORT", 1)};               // 1 = onesweep.cuh (default), 0 = depth_sort.cuh
 std::atomic<long long> g_launches{0};                             // kernels launched by this library (gsr_launch_count)
 #define GSR_LAUNCHED(n) g_launches.fetch_add((n), std::memory_order_relaxed)
@@ -124,6 +125,8 @@ int device_setup() {
   if (dev >= 0 && dev < 64 && done[dev].load(std::memory_order_acquire)) return GSR_OK;
   GSR_CUDA(cudaFuncSetAttribute(bin_count_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)BINC_SMEM_MAX), "bin_count smem attribute");
+  GSR_CUDA(cudaFuncSetAttribute(preprocess_fwd_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, PFB_SMEM),
+           "preprocess_fwd_bulk smem attribute");
   if (dev >= 0 && dev < 64) done[dev].store(1, std::memory_order_release);
   return GSR_OK;
 }
@@ -191,6 +194,7 @@ int gsr_set_option(const char* name, int32_t value) {
   if (!strcmp(name, "bin_cta")) g_force_bin_cta.store(value < 0 ? -1 : (value != 0));
   else if (!strcmp(name, "sort")) g_sort.store(value != 0);
   else if (!strcmp(name, "render_fwd")) g_render_fwd.store(value == 1 ? 1 : 2);
+  else if (!strcmp(name, "pre_fwd")) g_pre_fwd.store(value == 1 ? 1 : 2);
   else if (!strcmp(name, "render_bwd")) g_render_bwd.store(value == 1 || value == 3 ? value : 2);
   else return fail(GSR_ERR_INVALID, std::string("gsr_set_option: unknown option ") + name);
   return GSR_OK;
@@ -318,7 +322,26 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   preprocess_fwd_staged_kernel<MT, STG><<<(in->P + PF_THREADS - 1) / PF_THREADS, PF_THREADS, 0, stream>>>(         \
       in->P, in->D, in->means3D, in->scales, in->rotations, in->opacities, in->sh, in->cov3D_precomp, cam,         \
       in->prefiltered, radii, g, im.ctrl)
-  if (staged_sh && in->M == 16) { if (stage_in) GSR_PFS_LAUNCH(16, true); else GSR_PFS_LAUNCH(16, false); }
+  const bool bulk = staged_sh && in->M == 16 && stage_in && in->scales && in->rotations && !in->cov3D_precomp &&
+                    aligned16(in->opacities) && in->P >= PF_THREADS && g_pre_fwd.load(std::memory_order_relaxed) == 2;
+  if (bulk) {
+    // full tiles: persistent kernel with bulk-asynchronous staging; the last partial tile: the one-tile kernel on
+    // pointers advanced to it
+    if (int rc = device_setup()) return rc;
+    const int n_tiles = in->P / PF_THREADS, tail = in->P - n_tiles * PF_THREADS;
+    preprocess_fwd_bulk_kernel<<<std::min(n_tiles, 148 * 3), PF_THREADS, PFB_SMEM, stream>>>(
+        n_tiles, in->D, in->means3D, in->scales, in->rotations, in->opacities, in->sh, cam, in->prefiltered, radii, g,
+        im.ctrl);
+    if (tail > 0) {
+      const size_t off = (size_t)n_tiles * PF_THREADS;
+      GeomView gt = g;
+      gt.g0 += off; gt.g1 += off; gt.g2 += off; gt.keys[0] += off;
+      preprocess_fwd_staged_kernel<16, true><<<1, PF_THREADS, 0, stream>>>(
+          tail, in->D, in->means3D + 3 * off, in->scales + 3 * off, in->rotations + 4 * off, in->opacities + off,
+          in->sh + 48 * off, nullptr, cam, in->prefiltered, radii + off, gt, im.ctrl);
+      GSR_LAUNCHED(1);
+    }
+  } else if (staged_sh && in->M == 16) { if (stage_in) GSR_PFS_LAUNCH(16, true); else GSR_PFS_LAUNCH(16, false); }
   else if (staged_sh) { if (stage_in) GSR_PFS_LAUNCH(4, true); else GSR_PFS_LAUNCH(4, false); }
   else if (vec_sh && stage_in) GSR_PF_LAUNCH(true, true);
   else if (vec_sh) GSR_PF_LAUNCH(true, false);

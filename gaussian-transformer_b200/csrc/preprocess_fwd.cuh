@@ -433,6 +433,133 @@ __global__ void __launch_bounds__(PF_THREADS, GSR_PF_MIN_CTAS) preprocess_fwd_st
   geom.g2[i] = o2;
 }
 
+// ------------------------------------------------------------------------------------------------------------------
+// Persistent variant with bulk-asynchronous staging (TMA 1-D bulk copies, SASS UBLKCP, completion on an mbarrier).
+// A CTA walks tiles of 128 consecutive Gaussians; while it computes tile k from one shared-memory stage, the five
+// input blocks of tile k + gridDim.x -- SH rows 128 x 192 B, means3D / scales 128 x 12 B, rotations 128 x 16 B,
+// opacities 128 x 4 B, each contiguous in global memory -- are already in flight into the other stage, issued by one
+// thread as five cp.async.bulk instructions.  So a CTA's bytes are in flight during its WHOLE life, not only while
+// its own geometry runs (the closed loop that held the one-tile-per-CTA kernel at ~4 TB/s).
+// Price: the SH rows of culled Gaussians are fetched too (14 % at config 2), and a thread reads its 192-byte row from
+// the linear tile with 4-way bank conflicts (the shared-memory pipe is otherwise idle here).
+// Used for full tiles when M = 16, scales + rotations given, and every array 16-byte aligned; the host launches the
+// one-tile kernel for the last partial tile.
+// MEASURED SLOWER than the one-tile kernel (85 vs 70 us at config 2, 208 vs 177 us at 3 M) and therefore not the
+// default (gsr_set_option("pre_fwd", 2) selects it): two 30 KB stages allow 3 CTAs = 12 warps per SM, and the geometry
+// half -- ~600 dependent instructions per Gaussian -- needs ~24 warps per SM to keep the issue slots busy; at 192 B of
+// SH per Gaussian shared memory cannot hold a second tile in flight for that many warps.  Kept as the record of the
+// experiment and as a bit-exact second implementation (tests/test_gpu_api.py).
+constexpr int PFB_STAGE_SH = PF_THREADS * 192, PFB_STAGE_MEAN = PF_THREADS * 12, PFB_STAGE_ROT = PF_THREADS * 16,
+              PFB_STAGE_OPAC = PF_THREADS * 4;
+constexpr int PFB_OFF_MEAN = PFB_STAGE_SH, PFB_OFF_SCALE = PFB_OFF_MEAN + PFB_STAGE_MEAN,
+              PFB_OFF_ROT = PFB_OFF_SCALE + PFB_STAGE_MEAN, PFB_OFF_OPAC = PFB_OFF_ROT + PFB_STAGE_ROT,
+              PFB_STAGE_BYTES = PFB_OFF_OPAC + PFB_STAGE_OPAC;  // 30,208
+constexpr int PFB_SMEM = 2 * PFB_STAGE_BYTES;
+
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t mbar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(mbar)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t mbar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred P1;\n"
+      "LAB_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+      "@P1 bra DONE;\n"
+      "bra LAB_WAIT;\n"
+      "DONE:\n"
+      "}\n" ::"r"(mbar),
+      "r"(parity)
+      : "memory");
+}
+
+__global__ void __launch_bounds__(PF_THREADS, 3) preprocess_fwd_bulk_kernel(
+    int n_tiles, int D, const float* __restrict__ means3D, const float* __restrict__ scales,
+    const float* __restrict__ rotations, const float* __restrict__ opacities, const float* __restrict__ shs, Cam cam,
+    int prefiltered, int* __restrict__ radii, GeomView geom, uint32_t* __restrict__ ctrl) {
+  extern __shared__ __align__(128) unsigned char pfb_smem[];
+  __shared__ __align__(8) unsigned long long s_mbar[2];
+  const int tid = threadIdx.x;
+  const uint32_t smem0 = (uint32_t)__cvta_generic_to_shared(pfb_smem);
+  const uint32_t mbar0 = (uint32_t)__cvta_generic_to_shared(s_mbar);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar0));
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(mbar0 + 8u));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  auto issue = [&](int tile, int stage) {  // one thread: arm the stage's barrier, then the five bulk copies
+    const uint32_t mb = mbar0 + 8u * stage, dst = smem0 + (uint32_t)stage * PFB_STAGE_BYTES;
+    const size_t g = (size_t)tile * PF_THREADS;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"((uint32_t)PFB_STAGE_BYTES)
+                 : "memory");
+    bulk_g2s(dst, shs + g * 48, PFB_STAGE_SH, mb);
+    bulk_g2s(dst + PFB_OFF_MEAN, means3D + g * 3, PFB_STAGE_MEAN, mb);
+    bulk_g2s(dst + PFB_OFF_SCALE, scales + g * 3, PFB_STAGE_MEAN, mb);
+    bulk_g2s(dst + PFB_OFF_ROT, rotations + g * 4, PFB_STAGE_ROT, mb);
+    bulk_g2s(dst + PFB_OFF_OPAC, opacities + g, PFB_STAGE_OPAC, mb);
+  };
+  if (tid == 0 && (int)blockIdx.x < n_tiles) issue(blockIdx.x, 0);
+  const int K = (D + 1) * (D + 1), c4 = (3 * K + 3) >> 2;
+  int it = 0;
+  for (int tile = blockIdx.x; tile < n_tiles; tile += gridDim.x, it++) {
+    const int stage = it & 1;
+    const int next = tile + gridDim.x;
+    if (tid == 0 && next < n_tiles) issue(next, stage ^ 1);  // that stage was released by the barrier below
+    mbar_wait(mbar0 + 8u * stage, (uint32_t)((it >> 1) & 1));
+    const unsigned char* st = pfb_smem + (size_t)stage * PFB_STAGE_BYTES;
+    const float* s_mean = reinterpret_cast<const float*>(st + PFB_OFF_MEAN);
+    const float* s_scale = reinterpret_cast<const float*>(st + PFB_OFF_SCALE);
+    const int i = tile * PF_THREADS + tid;
+    float m[3], sc[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) { m[k] = s_mean[3 * tid + k]; sc[k] = s_scale[3 * tid + k]; }
+    float4 q_in = reinterpret_cast<const float4*>(st + PFB_OFF_ROT)[tid];
+    float opac_in = reinterpret_cast<const float*>(st + PFB_OFF_OPAC)[tid];
+    if (cam.raw_params) apply_activations(opac_in, sc, q_in);
+    int out_radius = 0, tiles = 0;
+    float4 o0 = make_float4(0.f, 0.f, 0.f, 0.f), o1 = o0, o2 = o0;
+    float conx = 0.f, cony = 0.f, conz = 0.f;
+    if (pre_geometry(i, m[0], m[1], m[2], sc[0], sc[1], sc[2], q_in, nullptr, cam, prefiltered, ctrl, o0, conx, cony,
+                     conz, out_radius, tiles)) {
+      const float dx = m[0] - __ldg(cam.campos), dy = m[1] - __ldg(cam.campos + 1), dz = m[2] - __ldg(cam.campos + 2);
+      const float len = sqrtf(dx * dx + dy * dy + dz * dz);
+      float basis[16];
+      sh_basis(D, dx / len, dy / len, dz / len, basis);
+      const float4* row4 = reinterpret_cast<const float4*>(st) + tid * 12;
+      float acc[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+      for (int k4 = 0; k4 < 12; k4++) {
+        if (k4 < c4) {
+          const float4 v = row4[k4];
+          const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const int j = 4 * k4 + u;
+            if (j / 3 < K) acc[j % 3] = fmaf(basis[j / 3], e[u], acc[j % 3]);
+          }
+        }
+      }
+      const float rr = acc[0] + 0.5f, gg = acc[1] + 0.5f, bb = acc[2] + 0.5f;
+      const uint32_t clamped = (rr < 0.f ? 1u : 0u) | (gg < 0.f ? 2u : 0u) | (bb < 0.f ? 4u : 0u);
+      o1 = make_float4(conx, cony, conz, opac_in);
+      o2 = make_float4(rr < 0.f ? 0.f : rr, gg < 0.f ? 0.f : gg, bb < 0.f ? 0.f : bb,
+                       __uint_as_float(((uint32_t)tiles << 3) | clamped));
+    } else {
+      out_radius = 0;
+      o0 = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    radii[i] = out_radius;
+    geom.keys[0][i] = out_radius > 0 ? __float_as_uint(o0.z) : 0xffffffffu;
+    geom.g0[i] = o0;
+    geom.g1[i] = o1;
+    geom.g2[i] = o2;
+    __syncthreads();  // every thread is done with this stage before the next iteration's issue refills it
+  }
+}
+
 // DGR/cuda_rasterizer/rasterizer_impl.cu:54-66 checkFrustum
 __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ view,
                                     uint8_t* __restrict__ present) {

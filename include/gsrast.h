@@ -334,7 +334,8 @@ GSR_API int64_t gsr_launch_count(int reset);
 /* Development / test switches (process-wide).  "bin_cta": -1 = pick the scatter kernel by list size (default),
  * 0 / 1 = force bin_pass_kernel<true> / bin_scatter_cta_kernel; "render_bwd": 2 = two pixels per thread (default),
  * 1 = one, 3 = two + test counters (accepted pairs, and pairs whose accept/reject differs between the forward's expf
- * and the backward's ex2.approx alpha, as three uint64 behind the accumulators of bwd_scratch).  "render_fwd": 2 / 1 likewise for the forward blend; "sort": 1 = onesweep depth sort (default), 0 = the histogram / row-scan / scatter
+ * and the backward's ex2.approx alpha, as three uint64 behind the accumulators of bwd_scratch).  "render_fwd": 2 / 1 likewise for the forward blend; "pre_fwd": 1 = one tile per CTA (default), 2 = the persistent
+ * preprocess kernel with bulk-asynchronous (TMA) staging, measured slower; "sort": 1 = onesweep depth sort (default), 0 = the histogram / row-scan / scatter
  * sort.  Initial values come from the environment variables GSR_BIN_CTA / GSR_RENDER_BWD / GSR_SORT, read once at load. */
 GSR_API int gsr_set_option(const char* name, int32_t value);
 /* Self-test of the forward blend's packed expf (render_fwd.cuh expf2_exact) against expf for every float whose bit

@@ -457,3 +457,22 @@ def test_two_pixel_forward_equals_one_pixel_forward():
         assert torch.equal(a["final_T"].view(torch.int32), b["final_T"].view(torch.int32)), name
         c1, c2 = a["color"], b["color"]
         assert torch.equal(torch.nan_to_num(c1), torch.nan_to_num(c2)) and torch.equal(c1.isnan(), c2.isnan()), name
+
+
+def test_bulk_async_preprocess_equals_one_tile_kernel():
+    """preprocess_fwd_bulk_kernel (persistent CTAs, cp.async.bulk + mbarrier double buffering; option pre_fwd = 2)
+    against the default one-tile-per-CTA kernel: every forward output bit-identical, incl. a partial last tile."""
+    from diff_gaussian_rasterization import _lib
+    from util import ours_forward
+    for P, W, H in ((128 * 37 + 5, 320, 200), (128 * 500, 640, 360), (100, 160, 96)):
+        sc = S.scene_S(P, W, H, seed=41)
+        d = to_device(sc)
+        res = []
+        for v in (1, 2):
+            _lib.set_option("pre_fwd", v)
+            res.append(ours_forward(d))
+        _lib.set_option("pre_fwd", 1)
+        a, b = res
+        for k in ("radii", "means2D", "depths", "conic_opacity", "rgb", "clamped", "tiles_touched", "point_list",
+                  "ranges", "n_contrib", "color"):
+            assert torch.equal(torch.nan_to_num(a[k].float()), torch.nan_to_num(b[k].float())), (P, k)
