@@ -45,7 +45,7 @@ def parse():
                          "two-shot all-reduce of 44 B/Gaussian), the same exchange with NCCL (all-gather of 12 "
                          "B/Gaussian/view SH factors + all-reduce of 44 B/Gaussian), or one NCCL all-reduce of the "
                          "full 236 B/Gaussian")
-    ap.add_argument("--peer-gather", default="nccl", choices=("nccl", "copy", "fused"),
+    ap.add_argument("--peer-gather", default="push", choices=("nccl", "copy", "fused", "push"),
                     help="peer exchange: how the SH-factor records travel (gsr_dp.PeerExchange)")
     ap.add_argument("--multimem", action="store_true",
                     help="peer exchange: all-reduce through the allocation's NVSwitch multicast mapping "
@@ -291,7 +291,7 @@ def dp_check(step, t, dpix, rank, world, dev):
             "bar": {k: max(1e-3, 3.0 * float(e)) for k, e in zip(LEAVES, self_dev)}}
 
 
-def c3_record(rank, world, dev, steps=6, warmup=2, peer=True, multimem=True, gather="nccl"):
+def c3_record(rank, world, dev, steps=6, warmup=2, peer=True, multimem=True, gather="push"):
     """BASELINE configs[2] ("C3") next to the C2 line: 3 M Gaussians, a batch of 8 views on a 30-degree arc at
     1080p, STRONG scaling -- rank 0 alone renders all 8 views (t_1), then the batch is split over the N ranks with
     the gsr_dp exchange (t_N); efficiency = t_1 / (N * t_N).  Device time, max over ranks."""
@@ -581,7 +581,8 @@ def run_ours(args, rank, world, local_rank):
                    "SH factor records (12 B/Gaussian/view) gathered by %s and summed by our rebuild kernel; all-reduce "
                    "of 44 B/Gaussian by our %s kernel over the symmetric allocation"
                    % ({"nccl": "one NCCL all-gather", "copy": "peer-to-peer copies", "fused": "remote reads inside "
-                       "the rebuild kernel"}[args.peer_gather],
+                       "the rebuild kernel", "push": "our push kernel (NVLink stores into every peer's buffer)"}[
+                          args.peer_gather],
                       "NVSwitch multimem" if (peer is not None and peer.flat_mc) else "two-shot P2P"),
                    "P": P_GAUSS, "visible": V, "num_rendered": R, "W": WIDTH, "H": HEIGHT,
                    "l2": "inputs (236 MB) + scratch exceed the 126 MB L2; no explicit flush"},

@@ -774,6 +774,34 @@ int gsr_peer_allreduce(int32_t world, int32_t rank, const uint64_t* peer_ptrs, u
   return GSR_OK;
 }
 
+int gsr_peer_push(int32_t world, int32_t rank, const uint64_t* peer_dst_ptrs, const float* src, int64_t n_floats,
+                  int64_t slot_floats, int32_t max_ctas, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (world < 1 || world > PEER_MAX_RANKS || rank < 0 || rank >= world || n_floats < 0 || (n_floats & 3) ||
+      (slot_floats & 3) || slot_floats < n_floats)
+    return fail(GSR_ERR_INVALID, "gsr_peer_push: bad world / rank / sizes (multiples of 4 floats, slot >= block)");
+  if (n_floats == 0 || world == 1) return GSR_OK;
+  if (!peer_dst_ptrs || !src || !aligned16(src)) return fail(GSR_ERR_INVALID, "gsr_peer_push: bad pointer");
+  PeerBufs b;
+  memset(&b, 0, sizeof(b));
+  for (int p = 0; p < world; p++) {
+    if (!peer_dst_ptrs[p] || (peer_dst_ptrs[p] & 15u)) return fail(GSR_ERR_INVALID, "gsr_peer_push: bad peer pointer");
+    b.p[p] = (float4*)peer_dst_ptrs[p];
+  }
+  const size_t n4 = (size_t)n_floats / 4, slot4 = (size_t)slot_floats / 4;
+  const int cap = max_ctas > 0 ? max_ctas : 64;
+  const int blocks = (int)std::min<size_t>((n4 + 1023) / 1024, (size_t)cap);
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  switch (world) {
+    case 2: peer_push_kernel<2><<<blocks, 256, 0, stream>>>(b, rank, s4, n4, slot4), GSR_LAUNCHED(1); break;
+    case 4: peer_push_kernel<4><<<blocks, 256, 0, stream>>>(b, rank, s4, n4, slot4), GSR_LAUNCHED(1); break;
+    case 8: peer_push_kernel<8><<<blocks, 256, 0, stream>>>(b, rank, s4, n4, slot4), GSR_LAUNCHED(1); break;
+    default: return fail(GSR_ERR_INVALID, "gsr_peer_push: world must be 2, 4 or 8");
+  }
+  GSR_STAGE("peer_push", 0, stream);
+  return GSR_OK;
+}
+
 int gsr_sh_grad_from_peers(int32_t P, int32_t D, int32_t M, int32_t V, const float* means3D,
                            const uint64_t* view_ptrs, float* dL_dsh, int32_t accumulate, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;

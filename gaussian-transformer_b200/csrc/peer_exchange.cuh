@@ -83,6 +83,31 @@ __global__ void __launch_bounds__(256) peer_allreduce_multimem_kernel(float4* mc
   }
 }
 
+// All-gather by PUSH: this rank's block of n4 float4 is stored into slot `rank` of every peer's gather buffer
+// (dst.p[p] = base of peer p's buffer; slots are slot4 float4 apart).  Stores over NVLink are posted, so a few CTAs
+// saturate the links and the kernel can run beside preprocess_bwd; U loads in flight per thread.
+template <int WORLD>
+__global__ void __launch_bounds__(256) peer_push_kernel(PeerBufs dst, int rank, const float4* __restrict__ src,
+                                                        size_t n4, size_t slot4) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  constexpr int U = 4;
+  for (size_t i0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i0 < n4; i0 += U * stride) {
+    float4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; u++)
+      if (i0 + u * stride < n4) v[u] = __ldcs(src + i0 + u * stride);
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const size_t i = i0 + u * stride;
+      if (i < n4) {
+#pragma unroll
+        for (int p = 0; p < WORLD; p++)
+          if (p != rank) dst.p[p][(size_t)rank * slot4 + i] = v[u];
+      }
+    }
+  }
+}
+
 // dL_dsh[i] (+)= sum_v basis(normalize(mean_i - campos_v)) (x) f_v(i), f_v read from the peer that rendered view v.
 // M == 16, dL_dsh 16-byte aligned (rows leave through shared memory with coalesced 128-bit stores).
 template <int VB>  // views fetched per batch (independent remote loads in flight per thread)

@@ -40,7 +40,7 @@ EXPORTS = (
     "gsr_backward_blend", "gsr_backward_geometry", "gsr_backward_sh_factors",
     "gsr_adam_step", "gsr_forward", "gsr_backward_geometry_split",
     "gsr_activate", "gsr_activate_backward", "gsr_densification_stats", "gsr_launch_count", "gsr_set_option",
-    "gsr_sort_scratch_bytes", "gsr_sort_pairs", "gsr_peer_allreduce", "gsr_sh_grad_from_peers",
+    "gsr_sort_scratch_bytes", "gsr_sort_pairs", "gsr_peer_allreduce", "gsr_sh_grad_from_peers", "gsr_peer_push",
     "gsr_compact_scratch_bytes", "gsr_compact_indices", "gsr_gather_rows", "gsr_selftest_expf",
 )
 STAGES = ("preprocess_fwd", "depth_sort", "bin_count", "bin_scatter", "render_fwd", "render_bwd", "preprocess_bwd")
@@ -87,6 +87,7 @@ def load(path=LIB_PATH):
     u64p = ctypes.POINTER(ctypes.c_uint64)
     lib.gsr_peer_allreduce.argtypes = [i32, i32, u64p, ctypes.c_uint64, i64, vp]
     lib.gsr_sh_grad_from_peers.argtypes = [i32, i32, i32, i32, vp, u64p, vp, i32, vp]
+    lib.gsr_peer_push.argtypes = [i32, i32, u64p, vp, i64, i64, i32, vp]
     lib.gsr_sort_scratch_bytes.argtypes = [i32, szp]
     lib.gsr_sort_pairs.argtypes = [i32, vp, vp, vp, vp, vp, i32, vp]
     lib.gsr_launch_count.argtypes = [ctypes.c_int]

@@ -283,10 +283,11 @@ class PeerExchange:
     """Factor sink (buffer / emit protocol of diff_gaussian_rasterization) + FlatGrads over a symmetric allocation."""
 
     def __init__(self, n_views: int, P: int, shapes_small: Dict[str, Sequence[int]], device, rank: int, world: int,
-                 group=None, use_multimem: bool = True, gather: str = "nccl"):
-        """gather: how the peers' view records reach this rank -- "nccl" (one all-gather launched when this rank's
-        last view has emitted its factors; fastest at 8 GPUs), "copy" (peer-to-peer copies by the copy engines) or
-        "fused" (the rebuild kernel reads the peers' records in place over NVLink)."""
+                 group=None, use_multimem: bool = False, gather: str = "push"):
+        """gather: how the peers' view records reach this rank -- "push" (our kernel stores this rank's records into
+        every peer's gather buffer, launched when the last view has emitted its factors, beside preprocess_bwd;
+        fastest at 8 GPUs), "nccl" (one all-gather at the same point), "copy" (peer-to-peer copies by the copy
+        engines) or "fused" (the rebuild kernel reads the peers' records in place over NVLink)."""
         import ctypes
         import torch.distributed._symmetric_memory as symm
         self.n_views, self.P, self.rank, self.world = n_views, P, rank, world
@@ -294,10 +295,12 @@ class PeerExchange:
         self.counts = [len(shard_views(n_views, r, world)) for r in range(world)]
         self.slot = (3 * P + 4 + 3) & ~3  # floats per view record: P*3 factors, 3 camera floats, padding
         n_flat = FlatGrads.numel(shapes_small)
-        self.buf = symm.empty(self.per_rank * self.slot + n_flat, dtype=torch.float32, device=device)
+        block = self.per_rank * self.slot
+        n_gather = world * block if gather == "push" else 0  # peers store their record blocks here
+        self.buf = symm.empty(block + n_flat + n_gather, dtype=torch.float32, device=device)
         self.hdl = symm.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
         self.flat_off = self.per_rank * self.slot
-        self.flat = FlatGrads(shapes_small, device, flat=self.buf[self.flat_off:])
+        self.flat = FlatGrads(shapes_small, device, flat=self.buf[self.flat_off:self.flat_off + n_flat])
         self.n_flat = n_flat
         ptrs = [int(p) for p in self.hdl.buffer_ptrs]
         self.flat_ptrs = (ctypes.c_uint64 * world)(*[p + 4 * self.flat_off for p in ptrs])
@@ -307,8 +310,8 @@ class PeerExchange:
         # records in a local staging copy that the copy engines fill over NVLink (no SM is spent on the gather, and
         # it runs under preprocess_bwd, which is HBM bound; the rebuild -- HBM bound too -- then runs under the
         # all-reduce, which is link bound).
-        if gather not in ("nccl", "copy", "fused"):
-            raise ValueError("gather must be 'nccl', 'copy' or 'fused'")
+        if gather not in ("nccl", "copy", "fused", "push"):
+            raise ValueError("gather must be 'nccl', 'copy', 'fused' or 'push'")
         self.gather, self.group = gather, group
         pairs = [(j, r) for j in range(self.per_rank) for r in range(world) if j < self.counts[r]]
         remote = [(j, r) for (j, r) in pairs if r != rank]
@@ -322,12 +325,17 @@ class PeerExchange:
         elif gather == "nccl":
             self.gathered = torch.empty(world, self.per_rank * self.slot, dtype=torch.float32, device=device)
             where = {(j, r): self.gathered.data_ptr() + 4 * (r * self.per_rank + j) * self.slot for (j, r) in remote}
+        elif gather == "push":
+            g_off = self.flat_off + n_flat
+            self.push_ptrs = (ctypes.c_uint64 * world)(*[p + 4 * g_off for p in ptrs])
+            where = {(j, r): ptrs[rank] + 4 * (g_off + r * block + j * self.slot) for (j, r) in remote}
         else:
             where = {(j, r): ptrs[r] + 4 * j * self.slot for (j, r) in remote}
         views = [where.get((j, r), ptrs[rank] + 4 * j * self.slot) for (j, r) in pairs]
         self.view_ptrs = (ctypes.c_uint64 * max(len(views), 1))(*views)
         self.V = len(views)
         self.copy_streams = [torch.cuda.Stream(device=device, priority=-1) for _ in range(2)]
+        self.push_ctas = 64
         self.side = torch.cuda.Stream(device=device, priority=-1)  # must get SMs while preprocess_bwd is dispatched
         self.n = 0
         self._sh = None
@@ -359,6 +367,17 @@ class PeerExchange:
                                                group=self.group, async_op=True)
             with torch.cuda.stream(self.side):
                 work.wait()
+                _lib.check(_lib.lib.gsr_sh_grad_from_peers(self.P, degree, M, self.V, means3D.data_ptr(),
+                                                           self.view_ptrs, sh.data_ptr(), 0, self.side.cuda_stream))
+        elif self.gather == "push":
+            # our own all-gather: every rank stores its record block into every peer's gather buffer (posted NVLink
+            # stores from a few CTAs, beside preprocess_bwd), then a barrier, then the rebuild from local memory
+            self.side.wait_stream(cur)
+            with torch.cuda.stream(self.side):
+                block = self.per_rank * self.slot
+                _lib.check(_lib.lib.gsr_peer_push(self.world, self.rank, self.push_ptrs, self.buf.data_ptr(), block,
+                                                  block, self.push_ctas, self.side.cuda_stream))
+                self.hdl.barrier(channel=0)  # every rank's pushes have landed
                 _lib.check(_lib.lib.gsr_sh_grad_from_peers(self.P, degree, M, self.V, means3D.data_ptr(),
                                                            self.view_ptrs, sh.data_ptr(), 0, self.side.cuda_stream))
         else:

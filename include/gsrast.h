@@ -295,6 +295,11 @@ GSR_API int gsr_gather_rows(int32_t n_tables, const gsr_gather_table* tables, in
  * followed by the view's 3 camera-position floats. */
 GSR_API int gsr_peer_allreduce(int32_t world, int32_t rank, const uint64_t* peer_ptrs, uint64_t multicast_ptr,
                                int64_t n_floats, void* stream);
+/* gsr_peer_push: all-gather by push -- this rank's block of n_floats floats (src) is stored into slot `rank` (slots
+ * are slot_floats apart) of the gather buffer of every OTHER rank, peer_dst_ptrs[p] = address in this process of rank
+ * p's gather buffer (symmetric allocation).  At most max_ctas CTAs (0 = 64), so that it can run beside another kernel. */
+GSR_API int gsr_peer_push(int32_t world, int32_t rank, const uint64_t* peer_dst_ptrs, const float* src,
+                          int64_t n_floats, int64_t slot_floats, int32_t max_ctas, void* stream);
 GSR_API int gsr_sh_grad_from_peers(int32_t P, int32_t D, int32_t M, int32_t V, const float* means3D,
                                    const uint64_t* view_ptrs, float* dL_dsh, int32_t accumulate, void* stream);
 
