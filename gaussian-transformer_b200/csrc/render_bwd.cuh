@@ -192,6 +192,10 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
 // accum_rec (backward.cu:515-519) dotted with dL/dpixel and shifted by one list entry: the reference's value at entry j
 // is U after entry j+1 (the previous one in back-to-front order).
 constexpr int RB2_THREADS = 128;
+#ifndef GSR_RB2_CTAS
+#define GSR_RB2_CTAS 8
+#endif
+
 
 // Gather + tile-level cull + order-preserving compaction of up to 256 list entries by 128 threads (entries tid and
 // tid + 128).  Entry k of the batch is list position first - k (back to front).  s_warp: 8 ints.
@@ -282,7 +286,7 @@ __device__ __forceinline__ float rcp_approx(float x) {
 // counts, in counters[0..2], the accepted (pixel, Gaussian) pairs, the pairs the forward accepted but this kernel's
 // ex2.approx alpha rejects, and the reverse (defined deviation 4).
 template <bool COUNT>
-__global__ void __launch_bounds__(RB2_THREADS, COUNT ? 4 : 8) render_bwd2_kernel(
+__global__ void __launch_bounds__(RB2_THREADS, COUNT ? 4 : GSR_RB2_CTAS) render_bwd2_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
     const float* __restrict__ bg, const float4* __restrict__ g0, const float4* __restrict__ g1,
     const float4* __restrict__ g2, const float* __restrict__ colors_precomp, const float* __restrict__ final_T,
