@@ -128,10 +128,10 @@ def algorithmic_bytes(P, V, R, N, K, M):
 # the run's own V and R equal the capture's (N = 1); otherwise traffic is null.
 NCU_CAPTURE = {"V": 860991, "R": 12071224, "source": "profiles/r02_ncu_full_metrics.txt"}
 NCU_DRAM_BYTES_C2 = {
-    "preprocess_fwd": 232.95e6 + 42.25e6,
-    "render_fwd": 65.70e6 + 18.59e6,
-    "render_bwd": 117.31e6 + 6.87e6,
-    "preprocess_bwd": 285.00e6 + 242.51e6,
+    "preprocess_fwd": 236.03e6 + 37.63e6,
+    "render_fwd": 65.47e6 + 17.93e6,
+    "render_bwd": 116.66e6 + 6.51e6,
+    "preprocess_bwd": 285.04e6 + 244.50e6,
 }
 
 
