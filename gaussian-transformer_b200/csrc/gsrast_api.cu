@@ -713,6 +713,61 @@ int gsr_compact_indices(int32_t P, const uint8_t* mask, int32_t* idx_out, int32_
   return GSR_OK;
 }
 
+// ---- gsr_compact_indices without caller scratch and without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, serving loops).
+// The block counts live in a file-scope device array that every GPU loading the library holds until exit
+// (GSR_NOALLOC_SCRATCH_WORDS * 4 = 16,400 bytes).  All calls on one device share it: calls that overlap on the GPU
+// (different streams) race.  Nothing in it has to start at zero -- compact_count_kernel writes every word that the two
+// later kernels read -- so the previous call's contents are harmless.
+constexpr int32_t GSR_NOALLOC_MAX_P = 1 << 24;                            // == GSR_COMPACT_NOALLOC_MAX_P (gsrast.h)
+constexpr int GSR_NOALLOC_SCRATCH_WORDS = GSR_NOALLOC_MAX_P / CP_BLOCK + 4;
+static_assert(GSR_NOALLOC_MAX_P == GSR_COMPACT_NOALLOC_MAX_P, "header and library disagree on the no-alloc maximum");
+static __device__ __align__(256) uint32_t g_noalloc_block_counts[GSR_NOALLOC_SCRATCH_WORDS];
+
+namespace {
+// The array's name is only a host-side stand-in in host code: its device address is looked up once per device, with
+// that device current, and cached.
+int noalloc_scratch(uint32_t** out) {
+  static std::mutex mu;
+  static uint32_t* addr[64] = {};
+  int dev = 0;
+  GSR_CUDA(cudaGetDevice(&dev), "gsr_compact_indices_noalloc: cudaGetDevice");
+  std::lock_guard<std::mutex> lk(mu);
+  if (dev >= 0 && dev < 64 && addr[dev]) {
+    *out = addr[dev];
+    return GSR_OK;
+  }
+  uint32_t* p = nullptr;
+  GSR_CUDA(cudaGetSymbolAddress((void**)&p, g_noalloc_block_counts), "gsr_compact_indices_noalloc: cudaGetSymbolAddress");
+  if (!p) return fail(GSR_ERR_CUDA, "gsr_compact_indices_noalloc: cudaGetSymbolAddress returned NULL");
+  if (dev >= 0 && dev < 64) addr[dev] = p;
+  *out = p;
+  return GSR_OK;
+}
+}  // namespace
+
+int gsr_compact_indices_noalloc(int32_t P, const uint8_t* mask, int32_t* idx_out, int32_t add, int64_t* count_out,
+                                void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (P < 0 || !count_out) return fail(GSR_ERR_INVALID, "gsr_compact_indices_noalloc: bad arguments");
+  if (P > GSR_NOALLOC_MAX_P)
+    return fail(GSR_ERR_INVALID, "gsr_compact_indices_noalloc: P = " + std::to_string(P) + " exceeds the built-in scratch (" +
+                                     std::to_string(GSR_NOALLOC_MAX_P) + " mask entries); use gsr_compact_indices");
+  if (P == 0) {
+    GSR_CUDA(cudaMemsetAsync(count_out, 0, 8, stream), "compact count memset");
+    return GSR_OK;
+  }
+  if (!mask || !idx_out) return fail(GSR_ERR_INVALID, "gsr_compact_indices_noalloc: NULL pointer");
+  uint32_t* counts = nullptr;
+  if (int rc = noalloc_scratch(&counts)) return rc;
+  const int nb = (P + CP_BLOCK - 1) / CP_BLOCK;
+  compact_count_kernel<<<nb, CP_THREADS, 0, stream>>>(P, mask, counts), GSR_LAUNCHED(1);
+  compact_offsets_kernel<<<1, 1024, 0, stream>>>(nb, counts, (unsigned long long*)count_out), GSR_LAUNCHED(1);
+  compact_write_kernel<<<nb, CP_THREADS, 0, stream>>>(P, mask, counts, idx_out, add), GSR_LAUNCHED(1);
+  GSR_STAGE("compact_indices_noalloc", 0, stream);
+  return GSR_OK;
+}
+
 int gsr_gather_rows(int32_t n_tables, const gsr_gather_table* tables, int64_t n_rows, const int32_t* idx,
                     void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;

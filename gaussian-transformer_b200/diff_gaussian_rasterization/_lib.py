@@ -41,7 +41,8 @@ EXPORTS = (
     "gsr_adam_step", "gsr_forward", "gsr_backward_geometry_split",
     "gsr_activate", "gsr_activate_backward", "gsr_densification_stats", "gsr_launch_count", "gsr_set_option",
     "gsr_sort_scratch_bytes", "gsr_sort_pairs", "gsr_peer_allreduce", "gsr_sh_grad_from_peers", "gsr_peer_push",
-    "gsr_compact_scratch_bytes", "gsr_compact_indices", "gsr_gather_rows", "gsr_selftest_expf",
+    "gsr_compact_scratch_bytes", "gsr_compact_indices", "gsr_compact_indices_noalloc", "gsr_gather_rows",
+    "gsr_selftest_expf",
 )
 STAGES = ("preprocess_fwd", "depth_sort", "bin_count", "bin_scatter", "render_fwd", "render_bwd", "preprocess_bwd")
 
@@ -83,6 +84,7 @@ def load(path=LIB_PATH):
     lib.gsr_selftest_expf.argtypes = [ctypes.c_uint32, ctypes.c_uint32, vp, vp]
     lib.gsr_compact_scratch_bytes.argtypes = [i32, szp]
     lib.gsr_compact_indices.argtypes = [i32, vp, vp, i32, vp, vp, vp]
+    lib.gsr_compact_indices_noalloc.argtypes = [i32, vp, vp, i32, vp, vp]
     lib.gsr_gather_rows.argtypes = [i32, vp, i64, vp, vp]
     u64p = ctypes.POINTER(ctypes.c_uint64)
     lib.gsr_peer_allreduce.argtypes = [i32, i32, u64p, ctypes.c_uint64, i64, vp]

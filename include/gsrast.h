@@ -280,6 +280,16 @@ typedef struct gsr_gather_table {
 GSR_API int gsr_compact_scratch_bytes(int32_t P, size_t* bytes);
 GSR_API int gsr_compact_indices(int32_t P, const uint8_t* mask, int32_t* idx_out, int32_t add, int64_t* count_out,
                                 void* scratch, void* stream);
+/* gsr_compact_indices with built-in scratch: allocates NOTHING (no cudaMalloc / cudaFree, no allocating library call),
+ * for callers that cannot allocate (CUDA graph capture, tight serving loops).  No counterpart in the reference.
+ * Same arguments and results as gsr_compact_indices minus `scratch`; the
+ * block counts live in a static device array of 16,400 bytes that every GPU loading the library holds until exit.
+ * P > GSR_COMPACT_NOALLOC_MAX_P is rejected with GSR_ERR_INVALID.  All calls on a device share the array (it keeps
+ * the last call's contents; nothing in it needs to start at zero): calls that overlap on the GPU race -- issue them
+ * on one stream or order them with events. */
+#define GSR_COMPACT_NOALLOC_MAX_P (1 << 24)
+GSR_API int gsr_compact_indices_noalloc(int32_t P, const uint8_t* mask, int32_t* idx_out, int32_t add,
+                                        int64_t* count_out, void* stream);
 GSR_API int gsr_gather_rows(int32_t n_tables, const gsr_gather_table* tables, int64_t n_rows, const int32_t* idx,
                             void* stream);
 
