@@ -389,4 +389,20 @@ __global__ void __launch_bounds__(1024) tile_scan_kernel(int T, const uint32_t* 
   }
 }
 
+// Sync-free forward (gsr_forward_capacity): when num_rendered does not fit the caller's list capacity the scatter and
+// the blend do nothing (their guard); this empties every tile's range as well, so that a backward launched without
+// the host having looked at num_rendered walks no list at all instead of reading past the buffer.
+__global__ void __launch_bounds__(256) void_ranges_on_overflow_kernel(int T, uint2* __restrict__ ranges,
+                                                                      const uint32_t* __restrict__ ctrl, uint32_t cap,
+                                                                      long long* __restrict__ result) {
+  if (blockIdx.x == 0 && threadIdx.x == 0) {  // {num_rendered, flags}: device memory or device-mapped pinned host memory
+    result[0] = (long long)(((unsigned long long)ctrl[CTRL_R_HI] << 32) | ctrl[CTRL_R_LO]);
+    result[1] = (long long)ctrl[CTRL_FLAGS];
+    __threadfence_system();
+  }
+  if (ctrl[CTRL_R_HI] == 0u && ctrl[CTRL_R_LO] <= cap) return;
+  const int t = blockIdx.x * 256 + threadIdx.x;
+  if (t < T) ranges[t] = make_uint2(0u, 0u);
+}
+
 }  // namespace gsr

@@ -110,8 +110,13 @@ int env_switch(const char* name, int dflt) {
   return (v && v[0] >= '0' && v[0] <= '9') ? atoi(v) : dflt;
 }
 std::atomic<int> g_force_bin_cta{env_switch("GSR_BIN_CTA", -1)};  // -1 = by list size, 0 / 1 = forced
-std::atomic<int> g_render_bwd{env_switch("GSR_RENDER_BWD", 2)};   // 1 = one pixel per thread, 2 = two (default)
-std::atomic<int> g_render_fwd{env_switch("GSR_RENDER_FWD", 2)};   // 1 = one pixel per thread, 2 = two (default)
+// blend kernels: 1 = one pixel per thread, 2 = two (default).  Backward: with 2, tile grids of at most g_pair_tiles tiles
+// take the PAIR instantiation (two list entries per step of the hit loop; measured on config C1, 1450 tiles with lists
+// of up to 650 entries: 150 -> 130 us, neutral within 3 % on evenly filled small grids, slower on large ones);
+// 4 = PAIR forced, 5 = PAIR off, 3 = the counting test kernel
+std::atomic<int> g_render_bwd{env_switch("GSR_RENDER_BWD", 2)};
+std::atomic<int> g_render_fwd{env_switch("GSR_RENDER_FWD", 2)};
+std::atomic<int> g_pair_tiles{env_switch("GSR_PAIR_TILES", 2048)};
 std::atomic<int> g_pre_fwd{env_switch("GSR_PRE_FWD", 1)};         // 1 = one tile per CTA (default), 2 = persistent bulk-copy kernel
 std::atomic<int> g_sort{env_switch("GSR_SORT", 1)};               // 1 = onesweep.cuh (default), 0 = depth_sort.cuh
 std::atomic<long long> g_launches{0};                             // kernels launched by this library (gsr_launch_count)
@@ -194,8 +199,9 @@ int gsr_set_option(const char* name, int32_t value) {
   if (!strcmp(name, "bin_cta")) g_force_bin_cta.store(value < 0 ? -1 : (value != 0));
   else if (!strcmp(name, "sort")) g_sort.store(value != 0);
   else if (!strcmp(name, "render_fwd")) g_render_fwd.store(value == 1 ? 1 : 2);
+  else if (!strcmp(name, "pair_tiles")) g_pair_tiles.store(value < 0 ? 0 : value);
   else if (!strcmp(name, "pre_fwd")) g_pre_fwd.store(value == 1 ? 1 : 2);
-  else if (!strcmp(name, "render_bwd")) g_render_bwd.store(value == 1 || value == 3 ? value : 2);
+  else if (!strcmp(name, "render_bwd")) g_render_bwd.store(value == 1 || (value >= 3 && value <= 5) ? value : 2);
   else return fail(GSR_ERR_INVALID, std::string("gsr_set_option: unknown option ") + name);
   return GSR_OK;
 }
@@ -285,8 +291,10 @@ int gsr_mark_visible(int32_t P, const float* means3D, const float* viewmatrix, c
   return GSR_OK;
 }
 
-int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radii, int64_t* host_result,
-                    void* stream_) {
+// copy_result = false (gsr_forward_capacity): num_rendered and the flags stay in ctrl[]; the caller's next kernel
+// delivers them
+static int forward_pre_impl(const gsr_inputs* in, void* geom, void* image, int32_t* radii, int64_t* host_result,
+                            void* stream_, bool copy_result) {
   cudaStream_t stream = (cudaStream_t)stream_;
   if (int rc = check_inputs(in)) return rc;
   if (!host_result) return fail(GSR_ERR_INVALID, "host_result is NULL");
@@ -396,8 +404,14 @@ int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radi
   }
   // ctrl[CTRL_R_LO..HI] -> host_result[0] (little endian int64), flags -> [1]
   static_assert(CTRL_R_HI == CTRL_R_LO + 1 && CTRL_FLAGS == CTRL_R_LO + 2, "ctrl words 4..7 = R, flags, 0");
-  GSR_CUDA(cudaMemcpyAsync(host_result, im.ctrl + CTRL_R_LO, 16, cudaMemcpyDeviceToHost, stream), "copy R, flags");
+  if (copy_result)
+    GSR_CUDA(cudaMemcpyAsync(host_result, im.ctrl + CTRL_R_LO, 16, cudaMemcpyDeviceToHost, stream), "copy R, flags");
   return GSR_OK;
+}
+
+int gsr_forward_pre(const gsr_inputs* in, void* geom, void* image, int32_t* radii, int64_t* host_result,
+                    void* stream_) {
+  return forward_pre_impl(in, geom, image, radii, host_result, stream_, true);
 }
 
 }  // extern "C"
@@ -509,7 +523,34 @@ int gsr_forward(const gsr_inputs* in, void* geom, void* binning, int64_t capacit
   return GSR_OK;
 }
 
-// Backward stage 1: per-pixel alpha-blending backward into the per-Gaussian accumulators of bwd_scratch.
+// The forward without any host synchronisation (CUDA-graph capturable, small-scene path): phase 1, then phase 2
+// against `capacity_R` list entries.  `result` receives {num_rendered, flags} by a store from a kernel on `stream`
+// (device memory, or pinned host memory, which the device addresses directly); the caller looks at it whenever it
+// next synchronises.  On overflow
+// (num_rendered > capacity_R) nothing is rendered and every tile range is emptied, so a backward launched blindly
+// with R = capacity_R is a no-op rather than an out-of-bounds walk.
+int gsr_forward_capacity(const gsr_inputs* in, void* geom, void* binning, int64_t capacity_R, void* image, int32_t* radii,
+                         int64_t* result, float* out_color, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  if (!in) return fail(GSR_ERR_INVALID, "gsr_inputs is NULL");
+  if (in->P <= 0) return fail(GSR_ERR_INVALID, "gsr_forward_capacity: P must be > 0");
+  if (capacity_R <= 0 || capacity_R > 0x7fffffffLL || !binning)
+    return fail(GSR_ERR_INVALID, "gsr_forward_capacity: needs a binning buffer of 0 < capacity_R <= 2^31-1 entries");
+  if (in->debug) return fail(GSR_ERR_INVALID, "gsr_forward_capacity: debug synchronises; use gsr_forward");
+  if (int rc = device_setup()) return rc;
+  if (!result) return fail(GSR_ERR_INVALID, "gsr_forward_capacity: result is NULL");
+  if (int rc = forward_pre_impl(in, geom, image, radii, result, stream_, false)) return rc;
+  const Cam cam = make_cam(in);
+  const size_t N = (size_t)in->W * in->H, T = (size_t)cam.gx * cam.gy;
+  ImageView im = image_view(image, N, T);
+  // delivers {num_rendered, flags} with a store from the device (a copy node between two kernels of a captured chain
+  // costs ~15 us of idle GPU) and empties the ranges on overflow
+  void_ranges_on_overflow_kernel<<<((int)T + 255) / 256, 256, 0, stream>>>((int)T, im.ranges, im.ctrl,
+                                                                          (uint32_t)capacity_R, (long long*)result), GSR_LAUNCHED(1);
+  GSR_STAGE("void_ranges_on_overflow", 0, stream);
+  return forward_post_impl(in, geom, binning, image, capacity_R, true, out_color, stream);
+}
+
 int gsr_backward_blend(const gsr_inputs* in, const void* geom, const void* binning, const void* image, int64_t R,
                        const float* dL_dpix, void* bwd_scratch, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -535,6 +576,11 @@ int gsr_backward_blend(const gsr_inputs* in, const void* geom, const void* binni
       render_bwd2_kernel<true><<<grid, RB2_THREADS, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0,
                                                                  g.g1, g.g2, in->colors_precomp, im.final_T,
                                                                  im.n_contrib, dL_dpix, bw, bw.counters), GSR_LAUNCHED(1);
+    else if (variant == 4 || (variant == 2 && (int)T <= g_pair_tiles.load(std::memory_order_relaxed)))
+      render_bwd2_kernel<false, true><<<grid, RB2_THREADS, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg,
+                                                                        g.g0, g.g1, g.g2, in->colors_precomp,
+                                                                        im.final_T, im.n_contrib, dL_dpix, bw, nullptr),
+          GSR_LAUNCHED(1);
     else
       render_bwd2_kernel<false><<<grid, RB2_THREADS, 0, stream>>>(im.ranges, b.point_list, in->W, in->H, in->bg, g.g0,
                                                                   g.g1, g.g2, in->colors_precomp, im.final_T,

@@ -285,8 +285,66 @@ __device__ __forceinline__ float rcp_approx(float x) {
 // COUNT (test instantiation, option render_bwd = 3): additionally evaluates the forward's exact alpha (expf) and
 // counts, in counters[0..2], the accepted (pixel, Gaussian) pairs, the pairs the forward accepted but this kernel's
 // ex2.approx alpha rejects, and the reverse (defined deviation 4).
-template <bool COUNT>
-__global__ void __launch_bounds__(RB2_THREADS, COUNT ? 4 : GSR_RB2_CTAS) render_bwd2_kernel(
+// ---- helpers of the PAIR instantiation (small scenes, see render_fwd2_kernel<true>): a list entry for the lane's two
+// pixels, split into (1) what depends on neither T nor U, (2) the recurrence on T and U with the nine sums it feeds
+// into the reduction, so that two entries' shared-memory loads, exponentials and reduce-scatter butterflies overlap.
+// Same operations as the loop body of the default instantiation.
+struct BwdHit2 {
+  float dx;
+  float2 dy, G, power;
+  float al0, al1;
+  float4 col;
+};
+__device__ __forceinline__ BwdHit2 bwd2_eval(uint32_t addr, float npx, float2 npy) {
+  BwdHit2 h;
+  const float4 a = lds128(addr);      // mean.x, mean.y, conic A, conic C
+  const float2 b = lds64(addr + 16);  // conic B, opacity
+  h.col = lds128(addr + 32);
+  h.dx = a.x + npx;
+  h.dy = __fadd2_rn(make_float2(a.y, a.y), npy);
+  const float dxA = h.dx * a.z, ndxB = -h.dx * b.x;
+  const float2 t1 = __fmul2_rn(h.dy, __fmul2_rn(h.dy, make_float2(a.w, a.w)));
+  const float2 s = __ffma2_rn(make_float2(h.dx, h.dx), make_float2(dxA, dxA), t1);
+  const float2 nv = __fmul2_rn(h.dy, make_float2(ndxB, ndxB));
+  h.power = __ffma2_rn(s, make_float2(-0.5f, -0.5f), nv);
+  const float2 pl = __fmul2_rn(h.power, make_float2(1.4426950408889634f, 1.4426950408889634f));
+  h.G = make_float2(ex2_approx(pl.x), ex2_approx(pl.y));
+  const float2 og = __fmul2_rn(make_float2(b.y, b.y), h.G);
+  h.al0 = fminf(0.99f, og.x);
+  h.al1 = fminf(0.99f, og.y);
+  return h;
+}
+struct BwdSums9 {
+  float v[9];
+};
+__device__ __forceinline__ BwdSums9 bwd2_step(const BwdHit2& h, bool v0, bool v1, float2& T, float2& U, float2 dLr,
+                                              float2 dLg, float2 dLb, float2 ntfbg) {
+  const float2 alpha = make_float2(v0 ? h.al0 : 0.f, v1 ? h.al1 : 0.f);
+  const float2 Ge = make_float2(v0 ? h.G.x : 0.f, v1 ? h.G.y : 0.f);
+  const float2 om = __ffma2_rn(alpha, make_float2(-1.f, -1.f), make_float2(1.f, 1.f));
+  const float2 rinv = make_float2(rcp_approx(om.x), rcp_approx(om.y));
+  T = __fmul2_rn(T, rinv);
+  const float2 cr = make_float2(h.col.x, h.col.x), cg = make_float2(h.col.y, h.col.y), cb = make_float2(h.col.z, h.col.z);
+  const float2 cd = __ffma2_rn(cb, dLb, __ffma2_rn(cg, dLg, __fmul2_rn(cr, dLr)));
+  const float2 cdU = __fadd2_rn(cd, make_float2(-U.x, -U.y));
+  const float2 dLda = __ffma2_rn(cdU, T, __fmul2_rn(ntfbg, rinv));
+  U = __ffma2_rn(alpha, cdU, U);
+  const float2 wgt = __fmul2_rn(alpha, T);
+  const float2 q = __fmul2_rn(Ge, dLda);
+  const float2 wr = __fmul2_rn(wgt, dLr), wg = __fmul2_rn(wgt, dLg), wb = __fmul2_rn(wgt, dLb);
+  const float2 qdy = __fmul2_rn(q, h.dy);
+  const float2 qdy2 = __fmul2_rn(qdy, h.dy);
+  const float qs = q.x + q.y, sy = qdy.x + qdy.y;
+  const float sx = h.dx * qs;
+  BwdSums9 r;
+  r.v[0] = wr.x + wr.y; r.v[1] = wg.x + wg.y; r.v[2] = wb.x + wb.y;
+  r.v[3] = qs; r.v[4] = sx; r.v[5] = sy; r.v[6] = h.dx * sx; r.v[7] = h.dx * sy; r.v[8] = qdy2.x + qdy2.y;
+  return r;
+}
+
+// PAIR (with COUNT = false only): the small-scene instantiation, two list entries per step of the hit loop.
+template <bool COUNT, bool PAIR = false>
+__global__ void __launch_bounds__(RB2_THREADS, (COUNT || PAIR) ? 4 : GSR_RB2_CTAS) render_bwd2_kernel(
     const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list, int W, int H,
     const float* __restrict__ bg, const float4* __restrict__ g0, const float4* __restrict__ g1,
     const float4* __restrict__ g2, const float* __restrict__ colors_precomp, const float* __restrict__ final_T,
@@ -358,6 +416,45 @@ __global__ void __launch_bounds__(RB2_THREADS, COUNT ? 4 : GSR_RB2_CTAS) render_
       unsigned mask = __ballot_sync(0xffffffffu, hit);
       const uint32_t chunk_addr = rec_addr + (uint32_t)c0 * (uint32_t)sizeof(StageRec);
       const uint32_t chunk_id_addr = id_addr + (uint32_t)c0 * 4u;
+      if constexpr (PAIR) {
+        while (mask) {
+          const uint32_t bitA = (uint32_t)(__ffs(mask) - 1);
+          mask &= mask - 1;
+          const bool two = mask != 0u;  // warp-uniform
+          const uint32_t bitB = two ? (uint32_t)(__ffs(mask) - 1) : bitA;
+          mask &= mask - 1;             // no-op on 0
+          const BwdHit2 hA = bwd2_eval(chunk_addr + bitA * (uint32_t)sizeof(StageRec), npx, npy);
+          const BwdHit2 hB = bwd2_eval(chunk_addr + bitB * (uint32_t)sizeof(StageRec), npx, npy);
+          const uint32_t posA = __float_as_uint(hA.col.w), posB = __float_as_uint(hB.col.w);
+          const bool vA0 = (posA < lc0) && !(hA.power.x > 0.0f) && !(hA.al0 < 1.0f / 255.0f);
+          const bool vA1 = (posA < lc1) && !(hA.power.y > 0.0f) && !(hA.al1 < 1.0f / 255.0f);
+          const bool vB0 = two && (posB < lc0) && !(hB.power.x > 0.0f) && !(hB.al0 < 1.0f / 255.0f);
+          const bool vB1 = two && (posB < lc1) && !(hB.power.y > 0.0f) && !(hB.al1 < 1.0f / 255.0f);
+          const bool anyA = __any_sync(0xffffffffu, vA0 || vA1), anyB = __any_sync(0xffffffffu, vB0 || vB1);
+          if (!(anyA || anyB)) continue;
+          // an entry no pixel accepts has alpha = 0 everywhere: T and U pass through unchanged, its sums are 0
+          const BwdSums9 sA = bwd2_step(hA, vA0, vA1, T, U, dLr, dLg, dLb, ntfbg);
+          const BwdSums9 sB = bwd2_step(hB, vB0, vB1, T, U, dLr, dLg, dLb, ntfbg);
+          if (anyA && anyB) {
+            const float sumA = warp_reduce_scatter9(sA.v[0], sA.v[1], sA.v[2], sA.v[3], sA.v[4], sA.v[5], sA.v[6],
+                                                    sA.v[7], sA.v[8], lane);
+            const float sumB = warp_reduce_scatter9(sB.v[0], sB.v[1], sB.v[2], sB.v[3], sB.v[4], sB.v[5], sB.v[6],
+                                                    sB.v[7], sB.v[8], lane);
+            const uint32_t offA = lds32(chunk_id_addr + bitA * 4u) << commit_shift;
+            const uint32_t offB = lds32(chunk_id_addr + bitB * 4u) << commit_shift;
+            if (commit >= 0) {
+              atomicAdd(commit_base + offA, sumA);
+              atomicAdd(commit_base + offB, sumB);
+            }
+          } else {
+            const BwdSums9& s1 = anyA ? sA : sB;
+            const float sum = warp_reduce_scatter9(s1.v[0], s1.v[1], s1.v[2], s1.v[3], s1.v[4], s1.v[5], s1.v[6],
+                                                   s1.v[7], s1.v[8], lane);
+            const uint32_t off = lds32(chunk_id_addr + (anyA ? bitA : bitB) * 4u) << commit_shift;
+            if (commit >= 0) atomicAdd(commit_base + off, sum);
+          }
+        }
+      } else
       while (mask) {
         const uint32_t bit = (uint32_t)(__ffs(mask) - 1);
         mask &= mask - 1;

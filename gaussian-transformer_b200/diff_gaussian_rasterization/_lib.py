@@ -38,7 +38,7 @@ EXPORTS = (
     "gsr_sh_color_factors", "gsr_sh_grad_from_factors", "gsr_knn_scratch_bytes", "gsr_knn_dist2",
     "gsr_loss_scratch_bytes", "gsr_l1_ssim_loss", "gsr_l1_ssim_backward",
     "gsr_backward_blend", "gsr_backward_geometry", "gsr_backward_sh_factors",
-    "gsr_adam_step", "gsr_forward", "gsr_backward_geometry_split",
+    "gsr_adam_step", "gsr_forward", "gsr_forward_capacity", "gsr_backward_geometry_split",
     "gsr_activate", "gsr_activate_backward", "gsr_densification_stats", "gsr_launch_count", "gsr_set_option",
     "gsr_sort_scratch_bytes", "gsr_sort_pairs", "gsr_peer_allreduce", "gsr_sh_grad_from_peers", "gsr_peer_push",
     "gsr_compact_scratch_bytes", "gsr_compact_indices", "gsr_compact_indices_noalloc", "gsr_gather_rows",
@@ -63,6 +63,7 @@ def load(path=LIB_PATH):
     lib.gsr_forward_pre.argtypes = [inp, vp, vp, vp, vp, vp]
     lib.gsr_forward_post.argtypes = [inp, vp, vp, vp, i64, vp, vp]
     lib.gsr_forward.argtypes = [inp, vp, vp, i64, vp, vp, vp, vp, vp]
+    lib.gsr_forward_capacity.argtypes = [inp, vp, vp, i64, vp, vp, vp, vp, vp]
     lib.gsr_backward.argtypes = [inp, vp, vp, vp, vp, i64, vp] + [vp] * 9 + [vp, vp]
     lib.gsr_backward_blend.argtypes = [inp, vp, vp, vp, i64, vp, vp, vp]
     lib.gsr_backward_geometry.argtypes = [inp, vp, vp] + [vp] * 9 + [vp, vp]

@@ -135,6 +135,16 @@ GSR_API int gsr_forward_post(const gsr_inputs* in, const void* geom, void* binni
 GSR_API int gsr_forward(const gsr_inputs* in, void* geom, void* binning, int64_t capacity_R, void* image,
                         int32_t* radii, int64_t* host_result, float* out_color, void* stream);
 
+/* gsr_forward without any host synchronisation, for CUDA-graph capture and small scenes where the num_rendered round
+ * trip and launch latency dominate (extension; the reference always waits for num_rendered,
+ * DGR/cuda_rasterizer/rasterizer_impl.cu:281).  `result` (int64[2] in device memory or in pinned host memory, which
+ * the device addresses directly) receives {num_rendered, flags} by a store from a kernel on `stream`.  capacity_R > 0 and binning are required, P > 0, debug = 0.  When
+ * num_rendered > capacity_R nothing is rendered and all tile ranges are emptied, so gsr_backward called with
+ * R = capacity_R is a harmless no-op; the caller detects the overflow from `result` after its next synchronisation
+ * and repeats the step with a larger buffer. */
+GSR_API int gsr_forward_capacity(const gsr_inputs* in, void* geom, void* binning, int64_t capacity_R, void* image,
+                                 int32_t* radii, int64_t* result, float* out_color, void* stream);
+
 /* Backward.  Replaces CudaRasterizer::Rasterizer::backward
  * (DGR/cuda_rasterizer/rasterizer_impl.cu:340-434; BACKWARD::render
  * backward.cu:399-557, computeCov2DCUDA :144-274, preprocessCUDA :346-396) and
@@ -338,7 +348,7 @@ enum {
   GSR_STAGE_BIN_COUNT = 2,      /* bin_count_cta_kernel (or bin_pass_kernel<false>), column_scan_kernel, tile_scan_kernel */
   GSR_STAGE_BIN_SCATTER = 3,    /* bin_pass_kernel<true> or bin_scatter_cta_kernel */
   GSR_STAGE_RENDER_FWD = 4,     /* render_fwd_kernel */
-  GSR_STAGE_RENDER_BWD = 5,     /* render_bwd2_kernel (render_bwd_kernel with option render_bwd = 1) */
+  GSR_STAGE_RENDER_BWD = 5,     /* render_bwd2_kernel<false, PAIR> (render_bwd_kernel with option render_bwd = 1) */
   GSR_STAGE_PREPROCESS_BWD = 6, /* preprocess_bwd_staged_kernel / preprocess_bwd_kernel */
   GSR_STAGE_COUNT = 7
 };
@@ -349,7 +359,9 @@ GSR_API int64_t gsr_launch_count(int reset);
 /* Development / test switches (process-wide).  "bin_cta": -1 = pick the scatter kernel by list size (default),
  * 0 / 1 = force bin_pass_kernel<true> / bin_scatter_cta_kernel; "render_bwd": 2 = two pixels per thread (default),
  * 1 = one, 3 = two + test counters (accepted pairs, and pairs whose accept/reject differs between the forward's expf
- * and the backward's ex2.approx alpha, as three uint64 behind the accumulators of bwd_scratch).  "render_fwd": 2 / 1 likewise for the forward blend; "pre_fwd": 1 = one tile per CTA (default), 2 = the persistent
+ * and the backward's ex2.approx alpha, as three uint64 behind the accumulators of bwd_scratch); with 2, tile grids of at
+ * most "pair_tiles" tiles (default 2048) run the instantiation that takes two list entries per step of its hit loop
+ * (small scenes with uneven lists: config C1 150 -> 130 us), 4 / 5 = that instantiation forced / never.  "render_fwd": 2 / 1 likewise for the forward blend; "pre_fwd": 1 = one tile per CTA (default), 2 = the persistent
  * preprocess kernel with bulk-asynchronous (TMA) staging, measured slower; "sort": 1 = onesweep depth sort (default), 0 = the histogram / row-scan / scatter
  * sort.  Initial values come from the environment variables GSR_BIN_CTA / GSR_RENDER_BWD / GSR_SORT, read once at load. */
 GSR_API int gsr_set_option(const char* name, int32_t value);

@@ -452,11 +452,32 @@ def test_two_pixel_forward_equals_one_pixel_forward():
             _lib.set_option("render_fwd", v)
             res.append(ours_forward(d))
         _lib.set_option("render_fwd", 2)
-        a, b = res
-        assert torch.equal(a["n_contrib"], b["n_contrib"]), name
-        assert torch.equal(a["final_T"].view(torch.int32), b["final_T"].view(torch.int32)), name
-        c1, c2 = a["color"], b["color"]
-        assert torch.equal(torch.nan_to_num(c1), torch.nan_to_num(c2)) and torch.equal(c1.isnan(), c2.isnan()), name
+        a = res[0]
+        for b in res[1:]:
+            assert torch.equal(a["n_contrib"], b["n_contrib"]), name
+            assert torch.equal(a["final_T"].view(torch.int32), b["final_T"].view(torch.int32)), name
+            c1, c2 = a["color"], b["color"]
+            assert torch.equal(torch.nan_to_num(c1), torch.nan_to_num(c2)) and torch.equal(c1.isnan(), c2.isnan()), name
+
+
+def test_pair_backward_equals_default_backward():
+    """render_bwd2_kernel<false, true> (small scenes: two list entries per step of the hit loop, option render_bwd = 4)
+    against the default instantiation (5 = PAIR off) on the same forward: same operations per entry, so the gradients
+    differ by the order of the atomics only."""
+    from diff_gaussian_rasterization import _lib
+    from test_gpu_parity import _check_grads
+    from util import ours_backward, ours_forward
+    for name in ("s_deg3", "s_big", "s_dense_opaque", "one_huge", "s_huge_lists", "c1_tiramisu"):
+        sc, _ = cases.case(name)
+        d = to_device(sc)
+        dpix = torch.from_numpy(S.upstream_grad(sc["W"], sc["H"], seed=7)).cuda()
+        fwd = ours_forward(d)
+        res = []
+        for v in (5, 4):
+            _lib.set_option("render_bwd", v)
+            res.append(ours_backward(d, fwd, dpix))
+        _lib.set_option("render_bwd", 2)
+        _check_grads(res[1], res[0], sc=sc)
 
 
 def test_bulk_async_preprocess_equals_one_tile_kernel():
