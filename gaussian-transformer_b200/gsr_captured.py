@@ -141,25 +141,29 @@ class CapturedRasterizer:
     def forward(self, check=True):
         """Replay the forward on the current stream -> (out_color, radii): the STATIC outputs, overwritten by the
         next replay.  check=True waits for num_rendered and repeats the step with a larger buffer if needed."""
-        if self._fwd_graph is None:
-            self.capture()
-        self._fwd_graph.replay()
-        if check:
-            self._done.record(torch.cuda.current_stream(self.dev))
-            self._done.synchronize()
-            ok, R = self.fits()
-            if not ok:
-                self.recaptures += 1
-                self.capture(capacity=2 * R + 65536)
-                self._fwd_graph.replay()
+        with torch.cuda.device(self.dev):
+            if self._fwd_graph is None:
+                self.capture()
+            self._fwd_graph.replay()
+            if check:
+                self._done.record(torch.cuda.current_stream(self.dev))
+                self._done.synchronize()
+                ok, R = self.fits()
+                if not ok:
+                    self.recaptures += 1
+                    self.capture(capacity=2 * R + 65536)
+                    self._fwd_graph.replay()
         return self.out_color, self.radii
 
     def backward(self, dL_dout=None):
         """Replay the backward of the last forward -> dict of the STATIC gradient tensors (means3D, means2D, sh,
         colors, opacity, scales, rot, cov3D, conic)."""
-        if dL_dout is not None and dL_dout.data_ptr() != self.dL_dout.data_ptr():
-            self.dL_dout.copy_(dL_dout)
-        self._bwd_graph.replay()
+        if self._bwd_graph is None:
+            raise RuntimeError("CapturedRasterizer.backward() before forward()")
+        with torch.cuda.device(self.dev):
+            if dL_dout is not None and dL_dout.data_ptr() != self.dL_dout.data_ptr():
+                self.dL_dout.copy_(dL_dout)
+            self._bwd_graph.replay()
         return self.grads
 
     def rasterize(self, means3D, sh, opacity, scales, rotations, check=True):
