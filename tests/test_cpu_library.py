@@ -20,6 +20,49 @@ def test_library_exports_every_declared_symbol():
     assert _lib.lib.gsr_compiled_arch() == 100 and _lib.lib.gsr_version() >= 100
 
 
+def _prototypes():
+    """{name: [parameter type strings]} of every GSR_API prototype in include/gsrast.h."""
+    hdr = open(os.path.join(ROOT, "include", "gsrast.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", " ", hdr, flags=re.S)
+    out = {}
+    for m in re.finditer(r"GSR_API\s+([\w\s\*]+?)\b(gsr_[a-z0-9_]+)\s*\(([^;]*?)\)\s*;", hdr, flags=re.S):
+        params = [q.strip() for q in m.group(3).split(",")]
+        out[m.group(2)] = [] if params in ([""], ["void"]) else params
+    return out
+
+
+def test_ctypes_argument_lists_match_the_header():
+    """A ctypes binding with a missing or mistyped argument corrupts the call silently: every export's argtypes must
+    have the prototype's number of parameters, pointers bound as pointers, floating-point scalars as the same
+    floating type and integer scalars as an integer of the same width."""
+    from diff_gaussian_rasterization import _lib
+    protos = _prototypes()
+    assert set(protos) == set(_lib.EXPORTS)
+    ints = {"int": 4, "int32_t": 4, "uint32_t": 4, "int64_t": 8, "uint64_t": 8, "size_t": 8}
+    for name, params in protos.items():
+        at = getattr(_lib.lib, name).argtypes
+        if at is None:
+            assert not params, f"{name}: no argtypes set for {len(params)} parameters"
+            continue
+        assert len(at) == len(params), (name, len(at), params)
+        for t, decl in zip(at, params):
+            base = re.sub(r"\b(const|struct)\b", "", decl).strip()
+            if "*" in base:
+                is_ptr = t in (ctypes.c_void_p, ctypes.c_char_p) or hasattr(t, "contents")
+                assert is_ptr, (name, decl, t)
+                continue
+            ctype = base.split()[0]
+            if ctype == "float":
+                assert t is ctypes.c_float, (name, decl, t)
+            elif ctype == "double":
+                assert t is ctypes.c_double, (name, decl, t)
+            else:
+                assert ctype in ints, (name, decl)
+                assert not hasattr(t, "contents") and t not in (ctypes.c_float, ctypes.c_double, ctypes.c_void_p), \
+                    (name, decl, t)
+                assert ctypes.sizeof(t) == ints[ctype], (name, decl, t)
+
+
 def test_scratch_bytes_and_error_reporting():
     from diff_gaussian_rasterization import _lib
     g, b, i, w = _lib.scratch_bytes(1_000_000, 5_000_000, 1920, 1080)
