@@ -63,6 +63,43 @@ def test_ctypes_argument_lists_match_the_header():
                 assert ctypes.sizeof(t) == ints[ctype], (name, decl, t)
 
 
+def test_header_is_plain_c_and_struct_layouts_match_ctypes(tmp_path):
+    """include/gsrast.h must compile as C99 (it is what a cgo / JNI / ctypes binding reads), and the ctypes mirrors of
+    its four structs must have the compiler's size and field offsets."""
+    import shutil
+    import subprocess
+    if shutil.which("gcc") is None:
+        pytest.skip("gcc not available")
+    import gsr_densify
+    import gsr_optim
+    from diff_gaussian_rasterization import _lib
+    mirrors = {"gsr_inputs": _lib.gsr_inputs, "gsr_views": _lib.gsr_views, "gsr_adam_group": gsr_optim._Group,
+               "gsr_gather_table": gsr_densify._Table}
+    lines = ['#include <stddef.h>', '#include <stdio.h>', '#include "gsrast.h"', "int main(void) {"]
+    for cname, mirror in mirrors.items():
+        lines.append('  printf("%s size %%zu\\n", sizeof(%s));' % (cname, cname))
+        for field, _ in mirror._fields_:
+            lines.append('  printf("%s %s %%zu\\n", offsetof(%s, %s));' % (cname, field, cname, field))
+    lines += ["  return 0;", "}"]
+    src = tmp_path / "layout.c"
+    src.write_text("\n".join(lines) + "\n")
+    exe = tmp_path / "layout"
+    subprocess.run(["gcc", "-std=c99", "-Wall", "-Werror", "-I", os.path.join(ROOT, "include"), str(src), "-o", str(exe)],
+                   check=True, capture_output=True)
+    got = {}
+    for line in subprocess.run([str(exe)], check=True, capture_output=True, text=True).stdout.splitlines():
+        cname, field, value = line.split()
+        got[(cname, field)] = int(value)
+    hdr = re.sub(r"/\*.*?\*/", " ", open(os.path.join(ROOT, "include", "gsrast.h")).read(), flags=re.S)
+    for cname, mirror in mirrors.items():
+        body = re.search(r"typedef\s+struct\s*\w*\s*\{([^}]*)\}\s*%s\s*;" % cname, hdr).group(1)
+        n_fields = sum(len(stmt.split(",")) for stmt in body.split(";") if stmt.strip())
+        assert n_fields == len(mirror._fields_), (cname, n_fields, len(mirror._fields_))
+        assert got[(cname, "size")] == ctypes.sizeof(mirror), cname
+        for field, _ in mirror._fields_:
+            assert got[(cname, field)] == getattr(mirror, field).offset, (cname, field)
+
+
 def test_scratch_bytes_and_error_reporting():
     from diff_gaussian_rasterization import _lib
     g, b, i, w = _lib.scratch_bytes(1_000_000, 5_000_000, 1920, 1080)
