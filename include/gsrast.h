@@ -363,7 +363,7 @@ GSR_API int64_t gsr_launch_count(int reset);
  * most "pair_tiles" tiles (default 2048) run the instantiation that takes two list entries per step of its hit loop
  * (small scenes with uneven lists: config C1 150 -> 130 us), 4 / 5 = that instantiation forced / never.  "render_fwd": 2 / 1 likewise for the forward blend; "pre_fwd": 1 = one tile per CTA (default), 2 = the persistent
  * preprocess kernel with bulk-asynchronous (TMA) staging, measured slower; "sort": 1 = onesweep depth sort (default), 0 = the histogram / row-scan / scatter
- * sort.  Initial values come from the environment variables GSR_BIN_CTA / GSR_RENDER_BWD / GSR_SORT, read once at load. */
+ * sort.  Initial values come from the environment variables GSR_BIN_CTA / GSR_RENDER_FWD / GSR_RENDER_BWD / GSR_PAIR_TILES / GSR_PRE_FWD / GSR_SORT, read once at load. */
 GSR_API int gsr_set_option(const char* name, int32_t value);
 /* Self-test of the forward blend's packed expf (render_fwd.cuh expf2_exact) against expf for every float whose bit
  * pattern lies in [lo_bits, hi_bits] and for its negation; *mismatches_device (device uint64) receives the count. */
